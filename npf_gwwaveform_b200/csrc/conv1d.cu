@@ -1,0 +1,381 @@
+// 1-D depth-separable residual conv blocks on channel-last tensors [B, L, C] (NPFK_MODE_FP32 parity path).
+//
+// Replaces BatchNorm1d -> ReLU -> Conv1d(groups=C) (+ residual) of ResConvBlock.forward
+// (reference npf/architectures/cnn.py:204-215; depth-separable wrapper npf/utils/helpers.py:354-403) and the
+// AvgPool1d / F.interpolate / cat glue of UnetCNN.apply_convs (cnn.py:451-490).  The reference permutes
+// NLC -> NCL around the CNN (cnn.py:363-375); here everything stays NLC so the channel index is the
+// coalesced one and the 1x1 convolutions are plain row-major Linear layers (npfk_linear_*).
+#include "common.cuh"
+
+namespace npfk {
+
+// ------------------------------------------------------------------------- batch statistics
+constexpr int kBnRows = 128;
+__global__ void bn_partial_kernel(const float* __restrict__ x, int64_t rows, int C, double* __restrict__ scratch) {
+    const int64_t r0 = (int64_t)blockIdx.x * kBnRows, r1 = min(rows, r0 + kBnRows);
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        double s = 0.0, ss = 0.0;
+        for (int64_t r = r0; r < r1; ++r) {
+            const double t = (double)x[r * C + c];
+            s += t;
+            ss += t * t;
+        }
+        atomicAdd(scratch + c, s);
+        atomicAdd(scratch + C + c, ss);
+    }
+}
+
+__global__ void bn_finalize_kernel(const double* __restrict__ scratch, int64_t rows, int C, float* __restrict__ stats,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var, float momentum) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const double n = (double)rows;
+    const double mean = scratch[c] / n;
+    double var = scratch[C + c] / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    stats[c] = (float)mean;
+    stats[C + c] = (float)var;
+    if (running_mean) {
+        const double unbiased = rows > 1 ? var * n / (n - 1.0) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    }
+}
+
+// ------------------------------------------------------------------------- depthwise conv forward
+constexpr int kDwMaxKs = 31;
+struct NormArgs {
+    const float* mean;    // NULL = no normalisation
+    const float* var;
+    const float* gamma;
+    const float* beta;
+    float eps;
+};
+
+__device__ __forceinline__ float pre_act(float x, float mean, float a, float beta, int relu) {
+    const float h = (x - mean) * a + beta;
+    return relu ? fmaxf(h, 0.f) : h;
+}
+
+// one thread per output element, channel fastest
+template <int KS>
+__global__ void __launch_bounds__(256)
+dwconv_fwd_kernel(const float* __restrict__ x, const NormArgs nrm, const float* __restrict__ w,
+                  const float* __restrict__ bias, const float* __restrict__ res, float* __restrict__ y, int B, int L,
+                  int C, int ks_rt, int relu) {
+    const int ks = KS > 0 ? KS : ks_rt;
+    const int pad = ks / 2;
+    const int64_t total = (int64_t)B * L * C;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(e % C);
+        const int64_t bl = e / C;
+        const int l = (int)(bl % L);
+        const int64_t b = bl / L;
+        float mean = 0.f, a = 1.f, beta = 0.f;
+        if (nrm.mean) {
+            mean = __ldg(nrm.mean + c);
+            a = __ldg(nrm.gamma + c) * rsqrtf(__ldg(nrm.var + c) + nrm.eps);
+            beta = __ldg(nrm.beta + c);
+        }
+        const float* xb = x + b * L * C + c;
+        float acc = bias ? __ldg(bias + c) : 0.f;
+#pragma unroll
+        for (int j = 0; j < (KS > 0 ? KS : kDwMaxKs); ++j) {
+            if (j < ks) {
+                const int li = l + j - pad;
+                if (li >= 0 && li < L)
+                    acc = fmaf(__ldg(w + c * ks + j), pre_act(__ldg(xb + (int64_t)li * C), mean, a, beta, relu), acc);
+            }
+        }
+        if (res) acc += __ldg(res + e);
+        y[e] = acc;
+    }
+}
+
+// ------------------------------------------------------------------------- depthwise conv backward
+// grid (C tiles of 128, L chunks, B); thread <-> channel, loops over the positions of its chunk.
+constexpr int kDwLChunk = 64;
+__global__ void __launch_bounds__(128)
+dwconv_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const NormArgs nrm,
+                  const float* __restrict__ w, float* __restrict__ dh, float* __restrict__ dw,
+                  float* __restrict__ dbias, float* __restrict__ sums, int L, int C, int ks, int relu) {
+    const int c = blockIdx.x * 128 + threadIdx.x;
+    if (c >= C) return;
+    const int b = blockIdx.z;
+    const int l0 = blockIdx.y * kDwLChunk, l1 = min(L, l0 + kDwLChunk);
+    const int pad = ks / 2;
+    float mean = 0.f, a = 1.f, beta = 0.f, invstd = 1.f;
+    if (nrm.mean) {
+        mean = __ldg(nrm.mean + c);
+        invstd = rsqrtf(__ldg(nrm.var + c) + nrm.eps);
+        a = __ldg(nrm.gamma + c) * invstd;
+        beta = __ldg(nrm.beta + c);
+    }
+    float wr[kDwMaxKs], dwacc[kDwMaxKs];
+#pragma unroll
+    for (int j = 0; j < kDwMaxKs; ++j) {
+        wr[j] = j < ks ? __ldg(w + c * ks + j) : 0.f;
+        dwacc[j] = 0.f;
+    }
+    const float* xb = x + (int64_t)b * L * C + c;
+    const float* dyb = dy + (int64_t)b * L * C + c;
+    float* dhb = dh + (int64_t)b * L * C + c;
+    float sb = 0.f, s1 = 0.f, s2 = 0.f;
+    for (int l = l0; l < l1; ++l) {
+        // gradient w.r.t. the activated input h[l]: correlate dy with the flipped kernel
+        float g = 0.f;
+#pragma unroll
+        for (int j = 0; j < kDwMaxKs; ++j) {
+            if (j < ks) {
+                const int lo = l - j + pad;   // output position that read h[l] through tap j
+                if (lo >= 0 && lo < L) g = fmaf(wr[j], __ldg(dyb + (int64_t)lo * C), g);
+            }
+        }
+        const float xv = __ldg(xb + (int64_t)l * C);
+        const float hpre = (xv - mean) * a + beta;
+        if (relu && !(hpre > 0.f)) g = 0.f;
+        dhb[(int64_t)l * C] = g;
+        s1 += g;
+        s2 = fmaf(g, (xv - mean) * invstd, s2);
+        // weight gradient: dw[j] += dy[l] * h[l + j - pad]
+        const float dyv = __ldg(dyb + (int64_t)l * C);
+        sb += dyv;
+#pragma unroll
+        for (int j = 0; j < kDwMaxKs; ++j) {
+            if (j < ks) {
+                const int li = l + j - pad;
+                if (li >= 0 && li < L)
+                    dwacc[j] = fmaf(dyv, pre_act(__ldg(xb + (int64_t)li * C), mean, a, beta, relu), dwacc[j]);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kDwMaxKs; ++j)
+        if (j < ks) atomicAdd(dw + c * ks + j, dwacc[j]);
+    if (dbias) atomicAdd(dbias + c, sb);
+    if (sums) {
+        atomicAdd(sums + c, s1);
+        atomicAdd(sums + C + c, s2);
+    }
+}
+
+__global__ void bn_bwd_kernel(const float* dh, const float* __restrict__ x, const float* __restrict__ mean,
+                              const float* __restrict__ var, const float* __restrict__ gamma, float eps,
+                              const float* __restrict__ sums, float* dx, float* __restrict__ dgamma,
+                              float* __restrict__ dbeta, int64_t rows, int C, int training) {
+    const int64_t total = rows * C;
+    const float inv_n = 1.f / (float)rows;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(e % C);
+        const float invstd = rsqrtf(__ldg(var + c) + eps);
+        const float a = __ldg(gamma + c) * invstd;
+        float g = dh[e];
+        if (training) {
+            const float xhat = (x[e] - __ldg(mean + c)) * invstd;
+            g = g - __ldg(sums + c) * inv_n - xhat * __ldg(sums + C + c) * inv_n;
+        }
+        dx[e] = a * g;
+    }
+    if (blockIdx.x == 0) {
+        for (int c = threadIdx.x; c < C; c += blockDim.x) {
+            dbeta[c] += sums[c];
+            dgamma[c] += sums[C + c];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------- pooling / upsampling / copies
+__global__ void avgpool2_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int B, int L, int C) {
+    const int Lo = L / 2;
+    const int64_t total = (int64_t)B * Lo * C;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(e % C);
+        const int64_t bl = e / C;
+        const int lo = (int)(bl % Lo);
+        const int64_t b = bl / Lo;
+        const float* p = x + (b * L + 2 * lo) * C + c;
+        y[e] = (p[0] + p[C]) * 0.5f;
+    }
+}
+
+__global__ void avgpool2_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int B, int L, int C) {
+    const int Lo = L / 2;
+    const int64_t total = (int64_t)B * L * C;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(e % C);
+        const int64_t bl = e / C;
+        const int l = (int)(bl % L);
+        const int64_t b = bl / L;
+        const int lo = l / 2;
+        dx[e] = lo < Lo ? 0.5f * dy[(b * Lo + lo) * C + c] : 0.f;
+    }
+}
+
+__device__ __forceinline__ void upsample_src(int lo, int L, int& i0, int& i1, float& lam) {
+    // align_corners=True: src = dst * (L-1)/(2L-1), evaluated in fp32 like ATen's area_pixel_compute_scale
+    const float scale = (2 * L > 1) ? (float)(L - 1) / (float)(2 * L - 1) : 0.f;
+    const float src = scale * (float)lo;
+    i0 = min((int)src, L - 1);
+    i1 = min(i0 + 1, L - 1);
+    lam = src - (float)i0;
+}
+
+__global__ void upsample2_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t ldy, int B, int L,
+                                     int C) {
+    const int Lo = 2 * L;
+    const int64_t total = (int64_t)B * Lo * C;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(e % C);
+        const int64_t bl = e / C;
+        const int lo = (int)(bl % Lo);
+        const int64_t b = bl / Lo;
+        int i0, i1;
+        float lam;
+        upsample_src(lo, L, i0, i1, lam);
+        const float* xb = x + b * L * C + c;
+        y[bl * ldy + c] = (1.f - lam) * xb[(int64_t)i0 * C] + lam * xb[(int64_t)i1 * C];
+    }
+}
+
+__global__ void upsample2_bwd_kernel(const float* __restrict__ dy, int64_t lddy, float* __restrict__ dx, int B, int L,
+                                     int C) {
+    const int Lo = 2 * L;
+    const int64_t total = (int64_t)B * Lo * C;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(e % C);
+        const int64_t bl = e / C;
+        const int lo = (int)(bl % Lo);
+        const int64_t b = bl / Lo;
+        int i0, i1;
+        float lam;
+        upsample_src(lo, L, i0, i1, lam);
+        const float g = dy[bl * lddy + c];
+        float* dxb = dx + b * L * C + c;
+        atomicAdd(dxb + (int64_t)i0 * C, (1.f - lam) * g);
+        atomicAdd(dxb + (int64_t)i1 * C, lam * g);
+    }
+}
+
+__global__ void copy2d_kernel(const float* __restrict__ src, int64_t lds, float* __restrict__ dst, int64_t ldd,
+                              int64_t rows, int cols) {
+    const int64_t total = rows * cols;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = e / cols;
+        const int c = (int)(e - r * cols);
+        dst[r * ldd + c] = src[r * lds + c];
+    }
+}
+
+inline unsigned ew_grid2(int64_t total, int block = 256) {
+    int64_t g = ceil_div64(total, block);
+    return (unsigned)max((int64_t)1, min(g, (int64_t)kNumSMs * 16));
+}
+
+}  // namespace npfk
+
+using namespace npfk;
+
+extern "C" {
+
+int npfk_bn_stats(const float* x, int64_t rows, int C, double* scratch, float* stats, float* running_mean,
+                  float* running_var, float momentum, void* stream) {
+    NPFK_REQUIRE(x && scratch && stats, "bn_stats: null pointer");
+    NPFK_REQUIRE(rows > 0 && C > 0, "bn_stats: bad shape");
+    NPFK_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_stats: running stats must come in pairs");
+    cudaStream_t st = as_stream(stream);
+    cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * C, st);
+    if (e != cudaSuccess) {
+        set_error("bn_stats: memset: %s", cudaGetErrorString(e));
+        return NPFK_ERR_CUDA;
+    }
+    NPFK_LAUNCH(bn_partial_kernel, (unsigned)ceil_div64(rows, kBnRows), 128, 0, st, x, rows, C, scratch);
+    int rc = check_launch("bn_partial");
+    if (rc != NPFK_OK) return rc;
+    NPFK_LAUNCH(bn_finalize_kernel, (C + 127) / 128, 128, 0, st, scratch, rows, C, stats, running_mean, running_var,
+                momentum);
+    return check_launch("bn_finalize");
+}
+
+int npfk_dwconv_fwd(const float* x, const float* mean, const float* var, const float* gamma, const float* beta,
+                    float eps, const float* w, const float* bias, const float* res, float* y, int B, int L, int C,
+                    int ks, int relu, void* stream) {
+    NPFK_REQUIRE(x && w && y, "dwconv_fwd: null pointer");
+    NPFK_REQUIRE(B > 0 && L > 0 && C > 0, "dwconv_fwd: bad shape");
+    NPFK_REQUIRE(ks > 0 && ks % 2 == 1 && ks <= kDwMaxKs, "dwconv_fwd: kernel size %d must be odd and <= %d", ks, kDwMaxKs);
+    NPFK_REQUIRE(!mean || (var && gamma && beta), "dwconv_fwd: incomplete normalisation arguments");
+    NormArgs n{mean, var, gamma, beta, eps};
+    const int64_t total = (int64_t)B * L * C;
+    cudaStream_t st = as_stream(stream);
+    const unsigned grid = ew_grid2(total);
+    switch (ks) {
+        case 5: NPFK_LAUNCH(dwconv_fwd_kernel<5>, grid, 256, 0, st, x, n, w, bias, res, y, B, L, C, ks, relu); break;
+        case 11: NPFK_LAUNCH(dwconv_fwd_kernel<11>, grid, 256, 0, st, x, n, w, bias, res, y, B, L, C, ks, relu); break;
+        case 19: NPFK_LAUNCH(dwconv_fwd_kernel<19>, grid, 256, 0, st, x, n, w, bias, res, y, B, L, C, ks, relu); break;
+        default: NPFK_LAUNCH(dwconv_fwd_kernel<0>, grid, 256, 0, st, x, n, w, bias, res, y, B, L, C, ks, relu); break;
+    }
+    return check_launch("dwconv_fwd");
+}
+
+int npfk_dwconv_bwd(const float* dy, const float* x, const float* mean, const float* var, const float* gamma,
+                    const float* beta, float eps, const float* w, float* dh, float* dw, float* dbias, float* sums,
+                    int B, int L, int C, int ks, int relu, void* stream) {
+    NPFK_REQUIRE(dy && x && w && dh && dw, "dwconv_bwd: null pointer");
+    NPFK_REQUIRE(B > 0 && B <= 65535 && L > 0 && C > 0, "dwconv_bwd: bad shape");
+    NPFK_REQUIRE(ks > 0 && ks % 2 == 1 && ks <= kDwMaxKs, "dwconv_bwd: kernel size %d must be odd and <= %d", ks, kDwMaxKs);
+    NPFK_REQUIRE(!mean || (var && gamma && beta), "dwconv_bwd: incomplete normalisation arguments");
+    NormArgs n{mean, var, gamma, beta, eps};
+    dim3 grid((C + 127) / 128, (L + kDwLChunk - 1) / kDwLChunk, B);
+    NPFK_LAUNCH(dwconv_bwd_kernel, grid, 128, 0, as_stream(stream), dy, x, n, w, dh, dw, dbias, sums, L, C, ks, relu);
+    return check_launch("dwconv_bwd");
+}
+
+int npfk_bn_bwd(const float* dh, const float* x, const float* mean, const float* var, const float* gamma, float eps,
+                const float* sums, float* dx, float* dgamma, float* dbeta, int64_t rows, int C, int training,
+                void* stream) {
+    NPFK_REQUIRE(dh && x && mean && var && gamma && sums && dx && dgamma && dbeta, "bn_bwd: null pointer");
+    if (rows * C <= 0) return NPFK_OK;
+    NPFK_LAUNCH(bn_bwd_kernel, ew_grid2(rows * C), 256, 0, as_stream(stream), dh, x, mean, var, gamma, eps, sums, dx,
+                dgamma, dbeta, rows, C, training);
+    return check_launch("bn_bwd");
+}
+
+int npfk_avgpool2_fwd(const float* x, float* y, int B, int L, int C, void* stream) {
+    NPFK_REQUIRE(x && y, "avgpool2_fwd: null pointer");
+    const int64_t total = (int64_t)B * (L / 2) * C;
+    if (total <= 0) return NPFK_OK;
+    NPFK_LAUNCH(avgpool2_fwd_kernel, ew_grid2(total), 256, 0, as_stream(stream), x, y, B, L, C);
+    return check_launch("avgpool2_fwd");
+}
+
+int npfk_avgpool2_bwd(const float* dy, float* dx, int B, int L, int C, void* stream) {
+    NPFK_REQUIRE(dy && dx, "avgpool2_bwd: null pointer");
+    const int64_t total = (int64_t)B * L * C;
+    if (total <= 0) return NPFK_OK;
+    NPFK_LAUNCH(avgpool2_bwd_kernel, ew_grid2(total), 256, 0, as_stream(stream), dy, dx, B, L, C);
+    return check_launch("avgpool2_bwd");
+}
+
+int npfk_upsample2_fwd(const float* x, float* y, int64_t ldy, int B, int L, int C, void* stream) {
+    NPFK_REQUIRE(x && y && ldy >= C, "upsample2_fwd: bad arguments");
+    const int64_t total = (int64_t)B * 2 * L * C;
+    if (total <= 0) return NPFK_OK;
+    NPFK_LAUNCH(upsample2_fwd_kernel, ew_grid2(total), 256, 0, as_stream(stream), x, y, ldy, B, L, C);
+    return check_launch("upsample2_fwd");
+}
+
+int npfk_upsample2_bwd(const float* dy, int64_t lddy, float* dx, int B, int L, int C, void* stream) {
+    NPFK_REQUIRE(dy && dx && lddy >= C, "upsample2_bwd: bad arguments");
+    const int64_t total = (int64_t)B * 2 * L * C;
+    if (total <= 0) return NPFK_OK;
+    NPFK_LAUNCH(upsample2_bwd_kernel, ew_grid2(total), 256, 0, as_stream(stream), dy, lddy, dx, B, L, C);
+    return check_launch("upsample2_bwd");
+}
+
+int npfk_copy2d(const float* src, int64_t lds, float* dst, int64_t ldd, int64_t rows, int cols, void* stream) {
+    NPFK_REQUIRE(src && dst && lds >= cols && ldd >= cols, "copy2d: bad arguments");
+    if (rows * cols <= 0) return NPFK_OK;
+    NPFK_LAUNCH(copy2d_kernel, ew_grid2(rows * cols), 256, 0, as_stream(stream), src, lds, dst, ldd, rows, cols);
+    return check_launch("copy2d");
+}
+
+}  // extern "C"

@@ -1,0 +1,275 @@
+// Row-wise helpers of the attentive / latent paths: residual + LayerNorm, broadcast merge, set mean.
+#include "common.cuh"
+
+namespace npfk {
+
+// ---------------------------------------------------------------- add + LayerNorm (one warp per row)
+template <int PL>  // values per lane: C <= 32*PL
+__global__ void __launch_bounds__(256)
+add_layernorm_fwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ gamma,
+                         const float* __restrict__ beta, float* __restrict__ out, float* __restrict__ mean,
+                         float* __restrict__ rstd, int64_t rows, int C, float eps) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = warp; row < rows; row += nwarps) {
+        float v[PL];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < PL; ++i) {
+            const int c = lane + 32 * i;
+            float t = 0.f;
+            if (c < C) {
+                t = a[row * C + c];
+                if (b) t += b[row * C + c];
+            }
+            v[i] = t;
+            s += t;
+        }
+        const float mu = warp_sum(s) / (float)C;
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < PL; ++i) {
+            const int c = lane + 32 * i;
+            const float d = (c < C) ? v[i] - mu : 0.f;
+            q = fmaf(d, d, q);
+        }
+        const float rs = rsqrtf(warp_sum(q) / (float)C + eps);
+#pragma unroll
+        for (int i = 0; i < PL; ++i) {
+            const int c = lane + 32 * i;
+            if (c < C) out[row * C + c] = (v[i] - mu) * rs * gamma[c] + beta[c];
+        }
+        if (lane == 0) {
+            mean[row] = mu;
+            rstd[row] = rs;
+        }
+    }
+}
+
+template <int PL>
+__global__ void __launch_bounds__(256)
+add_layernorm_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ a, const float* __restrict__ b,
+                         const float* __restrict__ gamma, const float* __restrict__ mean,
+                         const float* __restrict__ rstd, float* __restrict__ ds, float* __restrict__ dgamma,
+                         float* __restrict__ dbeta, int64_t rows, int C) {
+    __shared__ float sg[8][33];
+    __shared__ float sb[8][33];
+    const int lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    float accg[PL], accb[PL], gm[PL];
+#pragma unroll
+    for (int i = 0; i < PL; ++i) {
+        accg[i] = accb[i] = 0.f;
+        const int c = lane + 32 * i;
+        gm[i] = (c < C) ? gamma[c] : 0.f;
+    }
+    for (int64_t row = warp; row < rows; row += nwarps) {
+        const float mu = mean[row], rs = rstd[row];
+        float xh[PL], dxh[PL];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < PL; ++i) {
+            const int c = lane + 32 * i;
+            float t = 0.f, g = 0.f;
+            if (c < C) {
+                t = a[row * C + c];
+                if (b) t += b[row * C + c];
+                g = dout[row * C + c];
+                t = (t - mu) * rs;
+            }
+            xh[i] = t;
+            dxh[i] = g * gm[i];
+            accg[i] = fmaf(g, t, accg[i]);
+            accb[i] += g;
+            s1 += dxh[i];
+            s2 = fmaf(dxh[i], t, s2);
+        }
+        s1 = warp_sum(s1) / (float)C;
+        s2 = warp_sum(s2) / (float)C;
+#pragma unroll
+        for (int i = 0; i < PL; ++i) {
+            const int c = lane + 32 * i;
+            if (c < C) ds[row * C + c] = rs * (dxh[i] - s1 - xh[i] * s2);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < PL; ++i) {
+        sg[wl][lane] = accg[i];
+        sb[wl][lane] = accb[i];
+        __syncthreads();
+        const int c = lane + 32 * i;
+        if (wl == 0 && c < C) {
+            float tg = 0.f, tb = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+                tg += sg[w][lane];
+                tb += sb[w][lane];
+            }
+            atomicAdd(dgamma + c, tg);
+            atomicAdd(dbeta + c, tb);
+        }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------- out[z,b,t,:] = relu(a[b,t,:] + r[z,b,:])
+__global__ void bcast_add_relu_fwd_kernel(const float* __restrict__ a, const float* __restrict__ r,
+                                          float* __restrict__ out, int Z, int B, int64_t T, int C) {
+    const int64_t total = (int64_t)Z * B * T * C;
+    const int64_t btc = (int64_t)B * T * C, tc = T * C;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t z = e / btc, rem = e - z * btc;
+        const int64_t bb = rem / tc;
+        const int c = (int)(rem % C);
+        out[e] = fmaxf(a[rem] + r[(z * B + bb) * C + c], 0.f);
+    }
+}
+
+__global__ void bcast_add_relu_bwd_da_kernel(const float* __restrict__ dout, const float* __restrict__ out,
+                                             float* __restrict__ da, int Z, int64_t btc) {
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < btc; e += (int64_t)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < Z; ++z) {
+            const int64_t i = (int64_t)z * btc + e;
+            s += out[i] > 0.f ? dout[i] : 0.f;
+        }
+        da[e] = s;
+    }
+}
+
+constexpr int kBcastTChunk = 256;
+// grid (T chunks, B, Z); threads stride over C; dr[z,b,c] += sum_t
+__global__ void bcast_add_relu_bwd_dr_kernel(const float* __restrict__ dout, const float* __restrict__ out,
+                                             float* __restrict__ dr, int B, int64_t T, int C) {
+    const int z = blockIdx.z, b = blockIdx.y;
+    const int64_t t0 = (int64_t)blockIdx.x * kBcastTChunk, t1 = min(T, t0 + kBcastTChunk);
+    const int64_t base = ((int64_t)z * B + b) * T * C;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float s = 0.f;
+        for (int64_t t = t0; t < t1; ++t) {
+            const int64_t i = base + t * C + c;
+            s += out[i] > 0.f ? dout[i] : 0.f;
+        }
+        atomicAdd(dr + ((int64_t)z * B + b) * C + c, s);
+    }
+}
+
+// ---------------------------------------------------------------- mean over the set dimension
+// grid (B); 256 threads = 32 channel lanes x 8 row lanes
+__global__ void __launch_bounds__(256)
+set_mean_fwd_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t N, int C) {
+    __shared__ float sm[8][33];
+    const int b = blockIdx.x, lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
+    const float* xb = x + (int64_t)b * N * C;
+    for (int c0 = 0; c0 < C; c0 += 32) {
+        const int c = c0 + lane;
+        float s = 0.f;
+        if (c < C)
+            for (int64_t n = wl; n < N; n += 8) s += xb[n * C + c];
+        sm[wl][lane] = s;
+        __syncthreads();
+        if (wl == 0 && c < C) {
+            float t = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) t += sm[w][lane];
+            out[(int64_t)b * C + c] = t / (float)N;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void set_mean_bwd_kernel(const float* __restrict__ dout, float* __restrict__ dx, int B, int64_t N, int C) {
+    const int64_t total = (int64_t)B * N * C, nc = N * C;
+    const float inv = 1.f / (float)N;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = e / nc;
+        const int c = (int)(e % C);
+        dx[e] = dout[b * C + c] * inv;
+    }
+}
+
+inline unsigned ew_grid(int64_t total, int block = 256) {
+    int64_t g = ceil_div64(total, block);
+    return (unsigned)max((int64_t)1, min(g, (int64_t)kNumSMs * 16));
+}
+
+}  // namespace npfk
+
+using namespace npfk;
+
+extern "C" {
+
+int npfk_add_layernorm_fwd(const float* a, const float* b, const float* gamma, const float* beta, float* out,
+                           float* mean, float* rstd, int64_t rows, int C, float eps, void* stream) {
+    NPFK_REQUIRE(a && gamma && beta && out && mean && rstd, "add_layernorm_fwd: null pointer");
+    NPFK_REQUIRE(C > 0 && C <= 1024, "add_layernorm_fwd: C=%d outside (0,1024]", C);
+    if (rows <= 0) return NPFK_OK;
+    cudaStream_t st = as_stream(stream);
+    const unsigned grid = (unsigned)min(ceil_div64(rows, 8), (int64_t)kNumSMs * 8);
+    if (C <= 128) NPFK_LAUNCH(add_layernorm_fwd_kernel<4>, grid, 256, 0, st, a, b, gamma, beta, out, mean, rstd, rows, C, eps);
+    else if (C <= 256) NPFK_LAUNCH(add_layernorm_fwd_kernel<8>, grid, 256, 0, st, a, b, gamma, beta, out, mean, rstd, rows, C, eps);
+    else NPFK_LAUNCH(add_layernorm_fwd_kernel<32>, grid, 256, 0, st, a, b, gamma, beta, out, mean, rstd, rows, C, eps);
+    return check_launch("add_layernorm_fwd");
+}
+
+int npfk_add_layernorm_bwd(const float* dout, const float* a, const float* b, const float* gamma, const float* mean,
+                           const float* rstd, float* ds, float* dgamma, float* dbeta, int64_t rows, int C,
+                           void* stream) {
+    NPFK_REQUIRE(dout && a && gamma && mean && rstd && ds && dgamma && dbeta, "add_layernorm_bwd: null pointer");
+    NPFK_REQUIRE(C > 0 && C <= 1024, "add_layernorm_bwd: C=%d outside (0,1024]", C);
+    if (rows <= 0) return NPFK_OK;
+    cudaStream_t st = as_stream(stream);
+    const unsigned grid = (unsigned)min(ceil_div64(rows, 8 * 16), (int64_t)kNumSMs * 4);
+    if (C <= 128) NPFK_LAUNCH(add_layernorm_bwd_kernel<4>, grid, 256, 0, st, dout, a, b, gamma, mean, rstd, ds, dgamma, dbeta, rows, C);
+    else if (C <= 256) NPFK_LAUNCH(add_layernorm_bwd_kernel<8>, grid, 256, 0, st, dout, a, b, gamma, mean, rstd, ds, dgamma, dbeta, rows, C);
+    else NPFK_LAUNCH(add_layernorm_bwd_kernel<32>, grid, 256, 0, st, dout, a, b, gamma, mean, rstd, ds, dgamma, dbeta, rows, C);
+    return check_launch("add_layernorm_bwd");
+}
+
+int npfk_bcast_add_relu_fwd(const float* a, const float* r, float* out, int Z, int B, int64_t T, int C, void* stream) {
+    NPFK_REQUIRE(a && r && out, "bcast_add_relu_fwd: null pointer");
+    const int64_t total = (int64_t)Z * B * T * C;
+    if (total <= 0) return NPFK_OK;
+    NPFK_LAUNCH(bcast_add_relu_fwd_kernel, ew_grid(total), 256, 0, as_stream(stream), a, r, out, Z, B, T, C);
+    return check_launch("bcast_add_relu_fwd");
+}
+
+int npfk_bcast_add_relu_bwd(const float* dout, const float* out, float* da, float* dr, int Z, int B, int64_t T, int C,
+                            void* stream) {
+    NPFK_REQUIRE(dout && out, "bcast_add_relu_bwd: null pointer");
+    const int64_t btc = (int64_t)B * T * C;
+    if (btc * Z <= 0) return NPFK_OK;
+    cudaStream_t st = as_stream(stream);
+    int rc = NPFK_OK;
+    if (da) {
+        NPFK_LAUNCH(bcast_add_relu_bwd_da_kernel, ew_grid(btc), 256, 0, st, dout, out, da, Z, btc);
+        rc = check_launch("bcast_add_relu_bwd_da");
+        if (rc != NPFK_OK) return rc;
+    }
+    if (dr) {
+        NPFK_REQUIRE(B <= 65535 && Z <= 65535, "bcast_add_relu_bwd: B, Z must be <= 65535");
+        dim3 grid((unsigned)ceil_div64(T, kBcastTChunk), B, Z);
+        NPFK_LAUNCH(bcast_add_relu_bwd_dr_kernel, grid, min(C, 256), 0, st, dout, out, dr, B, T, C);
+        rc = check_launch("bcast_add_relu_bwd_dr");
+    }
+    return rc;
+}
+
+int npfk_set_mean_fwd(const float* x, float* out, int B, int64_t N, int C, void* stream) {
+    NPFK_REQUIRE(x && out, "set_mean_fwd: null pointer");
+    NPFK_REQUIRE(B > 0 && N > 0 && C > 0, "set_mean_fwd: bad shape");
+    NPFK_LAUNCH(set_mean_fwd_kernel, B, 256, 0, as_stream(stream), x, out, N, C);
+    return check_launch("set_mean_fwd");
+}
+
+int npfk_set_mean_bwd(const float* dout, float* dx, int B, int64_t N, int C, void* stream) {
+    NPFK_REQUIRE(dout && dx, "set_mean_bwd: null pointer");
+    const int64_t total = (int64_t)B * N * C;
+    if (total <= 0) return NPFK_OK;
+    NPFK_LAUNCH(set_mean_bwd_kernel, ew_grid(total), 256, 0, as_stream(stream), dout, dx, B, N, C);
+    return check_launch("set_mean_bwd");
+}
+
+}  // extern "C"

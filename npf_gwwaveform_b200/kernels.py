@@ -1,0 +1,609 @@
+"""autograd bindings of the npfk C-ABI (include/npfk.h).
+
+Every function here takes and returns CUDA fp32 tensors and launches hand-written sm_100a kernels on
+torch's current stream.  There is no fallback: CPU tensors or a missing libnpfk.so raise.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+from torch.autograd import Function
+
+from ._lib import LIB, NpfkError
+
+MODE_FP32 = 0
+MODE_FAST = 1
+
+_state = {"mode": MODE_FP32}
+
+
+def set_mode(mode) -> None:
+    """Select the arithmetic mode: "fp32" (<=1e-4 parity mode) or "fast" (tensor-core mode)."""
+    if isinstance(mode, str):
+        mode = {"fp32": MODE_FP32, "fast": MODE_FAST}[mode.lower()]
+    _state["mode"] = int(mode)
+
+
+def get_mode() -> int:
+    return _state["mode"]
+
+
+# ------------------------------------------------------------------------------------------ helpers
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _st():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def require_cuda(*ts) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise NpfkError(
+                "npf_gwwaveform_b200 runs on CUDA (sm_100a) tensors only; got a CPU tensor. "
+                "There is no CPU fallback for the npf hot path."
+            )
+
+
+def _c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """contiguous fp32 view/copy"""
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _rows_view(x: torch.Tensor):
+    """(tensor, ld) such that x can be read as M rows of K elements with row stride ld (no copy when possible)."""
+    K = x.shape[-1]
+    if x.dtype != torch.float32:
+        x = x.float()
+    if x.is_contiguous():
+        return x, K
+    ok = x.stride(-1) == 1 and x.dim() >= 2 and x.stride(-2) >= K
+    if ok:
+        for i in range(x.dim() - 2):
+            if x.shape[i] != 1 and x.stride(i) != x.stride(i + 1) * x.shape[i + 1]:
+                ok = False
+                break
+    if ok:
+        return x, x.stride(-2)
+    return x.contiguous(), K
+
+
+def _weight_view(w: torch.Tensor):
+    if w.dtype == torch.float32 and w.stride(1) == 1 and w.stride(0) >= w.shape[1]:
+        return w, w.stride(0)
+    w = w.float().contiguous()
+    return w, w.shape[1]
+
+
+# ------------------------------------------------------------------------------------------ Linear
+class _LinearFn(Function):
+    @staticmethod
+    def forward(ctx, x, w, b, res, relu: bool):
+        require_cuda(x, w, b, res)
+        N, K = w.shape
+        lead = x.shape[:-1]
+        xv, ldx = _rows_view(x)
+        wv, ldw = _weight_view(w)
+        M = 1
+        for s in lead:
+            M *= s
+        bv = _c(b)
+        resv = _c(res)
+        res_rows = 0
+        if resv is not None:
+            res_rows = resv.numel() // N
+            if res_rows == 0 or M % max(res_rows, 1) != 0:
+                raise NpfkError(f"linear: residual rows {res_rows} do not tile M={M}")
+        y = torch.empty(*lead, N, device=x.device, dtype=torch.float32)
+        if M > 0:
+            LIB.call("npfk_linear_fwd", _p(xv), ldx, _p(wv), ldw, _p(bv), _p(resv), N, res_rows, _p(y), N, M, N, K,
+                     int(relu), MODE_FP32, _st())
+        ctx.relu = relu
+        ctx.dims = (M, N, K, ldx, ldw, res_rows)
+        ctx.has_b = b is not None
+        ctx.has_res = res is not None
+        ctx.res_shape = None if res is None else res.shape
+        ctx.save_for_backward(xv, wv, y if relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xv, wv, y = ctx.saved_tensors
+        M, N, K, ldx, ldw, res_rows = ctx.dims
+        dy = _c(dy)
+        st = _st()
+        if ctx.relu and M > 0:
+            g = torch.empty_like(dy)
+            LIB.call("npfk_relu_bwd", _p(dy), N, _p(y), N, _p(g), N, M, N, st)
+        else:
+            g = dy
+        dx = dw = db = dres = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(*dy.shape[:-1], K, device=dy.device, dtype=torch.float32)
+            if M > 0:
+                LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wv), ldw, _p(dx), K, M, N, K, MODE_FP32, st)
+        need_w = ctx.needs_input_grad[1]
+        need_b = ctx.has_b and ctx.needs_input_grad[2]
+        if need_w or need_b:
+            dw = torch.zeros(N, K, device=dy.device, dtype=torch.float32)
+            db = torch.zeros(N, device=dy.device, dtype=torch.float32) if need_b else None
+            if M > 0:
+                LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(xv), ldx, _p(dw), K, _p(db), M, N, K, MODE_FP32, st)
+        if ctx.has_res and ctx.needs_input_grad[3]:
+            if res_rows == M:
+                dres = g.reshape(ctx.res_shape)
+            else:
+                dres = torch.empty(ctx.res_shape, device=dy.device, dtype=torch.float32)
+                LIB.call("npfk_rows_fold_sum", _p(g), N, _p(dres), N, res_rows, M // res_rows, N, st)
+        return dx, dw, db, dres, None
+
+
+def linear(x, w, b=None, res=None, relu=False):
+    """act(x @ w.T + b + res); `res` rows are tiled over the rows of x when it has fewer rows."""
+    return _LinearFn.apply(x, w, b, res, relu)
+
+
+# ------------------------------------------------------------------------------------------ broadcast merge
+class _BcastAddReluFn(Function):
+    @staticmethod
+    def forward(ctx, a, r):
+        # a:[B,T,C]  r:[Z,B,C] -> [Z,B,T,C]
+        require_cuda(a, r)
+        a, r = _c(a), _c(r)
+        B, T, C = a.shape
+        Z = r.shape[0]
+        out = torch.empty(Z, B, T, C, device=a.device, dtype=torch.float32)
+        LIB.call("npfk_bcast_add_relu_fwd", _p(a), _p(r), _p(out), Z, B, T, C, _st())
+        ctx.save_for_backward(out)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (out,) = ctx.saved_tensors
+        Z, B, T, C = out.shape
+        dout = _c(dout)
+        da = torch.empty(B, T, C, device=out.device, dtype=torch.float32) if ctx.needs_input_grad[0] else None
+        dr = torch.zeros(Z, B, C, device=out.device, dtype=torch.float32) if ctx.needs_input_grad[1] else None
+        LIB.call("npfk_bcast_add_relu_bwd", _p(dout), _p(out), _p(da), _p(dr), Z, B, T, C, _st())
+        return da, dr
+
+
+def bcast_add_relu(a, r):
+    return _BcastAddReluFn.apply(a, r)
+
+
+class _SetMeanFn(Function):
+    @staticmethod
+    def forward(ctx, x):
+        require_cuda(x)
+        x = _c(x)
+        B, N, C = x.shape
+        out = torch.empty(B, 1, C, device=x.device, dtype=torch.float32)
+        LIB.call("npfk_set_mean_fwd", _p(x), _p(out), B, N, C, _st())
+        ctx.shape = (B, N, C)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        B, N, C = ctx.shape
+        dout = _c(dout)
+        dx = torch.empty(B, N, C, device=dout.device, dtype=torch.float32)
+        LIB.call("npfk_set_mean_bwd", _p(dout), _p(dx), B, N, C, _st())
+        return dx
+
+
+def set_mean(x):
+    """mean over dim 1 with keepdim: [B,N,C] -> [B,1,C]"""
+    return _SetMeanFn.apply(x)
+
+
+# ------------------------------------------------------------------------------------------ attention
+class _MhaFn(Function):
+    @staticmethod
+    def forward(ctx, q, k, v, n_heads: int, scale: float):
+        require_cuda(q, k, v)
+        q, k, v = _c(q), _c(k), _c(v)
+        B, Nq, E = q.shape
+        Nk = k.shape[1]
+        D = E // n_heads
+        out = torch.empty_like(q)
+        lse = torch.empty(B, n_heads, Nq, device=q.device, dtype=torch.float32)
+        LIB.call("npfk_mha_fwd", _p(q), _p(k), _p(v), _p(out), _p(lse), B, Nq, Nk, n_heads, D, float(scale), _st())
+        ctx.save_for_backward(q, k, v, out, lse)
+        ctx.cfg = (B, Nq, Nk, n_heads, D, float(scale))
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q, k, v, out, lse = ctx.saved_tensors
+        B, Nq, Nk, H, D, scale = ctx.cfg
+        dout = _c(dout)
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        ws = torch.empty(B * H * Nq, device=q.device, dtype=torch.float32)
+        LIB.call("npfk_mha_bwd", _p(q), _p(k), _p(v), _p(out), _p(lse), _p(dout), _p(dq), _p(dk), _p(dv), _p(ws), B, Nq,
+                 Nk, H, D, scale, _st())
+        return dq, dk, dv, None, None
+
+
+def mha(q, k, v, n_heads: int, scale: float):
+    """softmax(q k^T * scale) v per head; heads are slices of the feature dim (no permutes)."""
+    return _MhaFn.apply(q, k, v, n_heads, scale)
+
+
+class _AddLayerNormFn(Function):
+    @staticmethod
+    def forward(ctx, a, b, gamma, beta, eps: float):
+        require_cuda(a, b, gamma, beta)
+        a, b, gamma, beta = _c(a), _c(b), _c(gamma), _c(beta)
+        C = a.shape[-1]
+        rows = a.numel() // C
+        out = torch.empty_like(a)
+        mean = torch.empty(rows, device=a.device, dtype=torch.float32)
+        rstd = torch.empty(rows, device=a.device, dtype=torch.float32)
+        LIB.call("npfk_add_layernorm_fwd", _p(a), _p(b), _p(gamma), _p(beta), _p(out), _p(mean), _p(rstd), rows, C,
+                 float(eps), _st())
+        ctx.save_for_backward(a, b, gamma, mean, rstd)
+        ctx.has_b = b is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        a, b, gamma, mean, rstd = ctx.saved_tensors
+        C = a.shape[-1]
+        rows = a.numel() // C
+        dout = _c(dout)
+        ds = torch.empty_like(a)
+        dg = torch.zeros_like(gamma)
+        db = torch.zeros_like(gamma)
+        LIB.call("npfk_add_layernorm_bwd", _p(dout), _p(a), _p(b), _p(gamma), _p(mean), _p(rstd), _p(ds), _p(dg), _p(db),
+                 rows, C, _st())
+        return ds, (ds if ctx.has_b else None), dg, db, None
+
+
+def add_layernorm(a, b, gamma, beta, eps=1e-5):
+    """LayerNorm(a + b) over the last dim"""
+    return _AddLayerNormFn.apply(a, b, gamma, beta, eps)
+
+
+# ------------------------------------------------------------------------------------------ SetConv
+class _SetConvRbfFn(Function):
+    @staticmethod
+    def forward(ctx, xk, xq, v, theta, p: float, unshared: bool):
+        # xk:[B,Nk,1] or [Nk] (shared grid)  xq:[B,Nq,1] or [Nq]  v:[B,Nk,C]  -> [B,Nq,C+1]
+        require_cuda(xk, xq, v, theta)
+        v, theta = _c(v), _c(theta)
+        B, Nk, C = v.shape
+        xk, sxk = _positions(xk, B, Nk)
+        xq, sxq = _positions(xq, B, None)
+        Nq = xq.numel() if sxq == 0 else xq.numel() // B
+        out = torch.empty(B, Nq, C + 1, device=v.device, dtype=torch.float32)
+        LIB.call("npfk_setconv_fwd", _p(xk), sxk, _p(xq), sxq, _p(v), _p(theta), _p(out), C + 1, B, Nk, Nq, C, float(p),
+                 int(unshared), _st())
+        ctx.save_for_backward(xk, xq, v, theta, out)
+        ctx.cfg = (sxk, sxq, B, Nk, Nq, C, float(p), int(unshared))
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xk, xq, v, theta, out = ctx.saved_tensors
+        sxk, sxq, B, Nk, Nq, C, p, unshared = ctx.cfg
+        dout = _c(dout)
+        dv = torch.zeros_like(v)
+        dtheta = torch.zeros_like(theta)
+        LIB.call("npfk_setconv_bwd", _p(xk), sxk, _p(xq), sxq, _p(v), _p(theta), _p(out), _p(dout), C + 1, _p(dv),
+                 _p(dtheta), B, Nk, Nq, C, p, unshared, _st())
+        return None, None, dv, dtheta, None, None
+
+
+def _positions(x, B, n):
+    """positions as a flat fp32 tensor + batch stride (0 when one grid is shared by the whole batch)"""
+    x = x.detach()
+    if x.dim() == 1:
+        return _c(x), 0
+    if x.dim() == 3 and x.shape[-1] == 1:
+        if x.stride(0) == 0:      # expanded grid
+            return _c(x[0, :, 0]), 0
+        x = _c(x)
+        return x, x.shape[1]
+    raise NpfkError(f"SetConv positions must be [N] or [B,N,1] (x_dim == 1); got {tuple(x.shape)}")
+
+
+def setconv_rbf(xk, xq, v, theta, p=2.0, unshared=False):
+    """cat(sum_k softmax-weights * v_k, density) with the exponential RBF; positions get no gradient."""
+    return _SetConvRbfFn.apply(xk, xq, v, theta, p, unshared)
+
+
+# ------------------------------------------------------------------------------------------ conv blocks
+class _NormActDwConvFn(Function):
+    """y = dwconv(act(norm(x))) + bias + res on channel-last [B,L,C]; BatchNorm statistics handled inside."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, w, bias, res, running_mean, running_var, training: bool, eps: float,
+                momentum: float, relu: bool):
+        require_cuda(x, w)
+        x, w = _c(x), _c(w)
+        B, L, C = x.shape
+        ks = w.shape[-1]
+        w2 = w.reshape(C, ks)
+        has_norm = gamma is not None
+        st = _st()
+        stats = None
+        mean = var = None
+        if has_norm:
+            gamma, beta = _c(gamma), _c(beta)
+            if training:
+                stats = torch.empty(2 * C, device=x.device, dtype=torch.float32)
+                scratch = torch.empty(2 * C, device=x.device, dtype=torch.float64)
+                LIB.call("npfk_bn_stats", _p(x), B * L, C, _p(scratch), _p(stats), _p(running_mean), _p(running_var),
+                         float(momentum), st)
+                mean, var = stats[:C], stats[C:]
+            else:
+                mean, var = _c(running_mean), _c(running_var)
+        bias_c, res_c = _c(bias), _c(res)
+        y = torch.empty_like(x)
+        LIB.call("npfk_dwconv_fwd", _p(x), _p(mean), _p(var), _p(gamma), _p(beta), float(eps), _p(w2), _p(bias_c),
+                 _p(res_c), _p(y), B, L, C, ks, int(relu), st)
+        ctx.save_for_backward(x, gamma, beta, w2, mean, var)
+        ctx.cfg = (B, L, C, ks, has_norm, bool(training), float(eps), bool(relu), bias is not None, res is not None,
+                   w.shape)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, beta, w2, mean, var = ctx.saved_tensors
+        B, L, C, ks, has_norm, training, eps, relu, has_bias, has_res, wshape = ctx.cfg
+        dy = _c(dy)
+        st = _st()
+        dev = x.device
+        dh = torch.empty_like(x)
+        dw = torch.zeros(C, ks, device=dev, dtype=torch.float32)
+        dbias = torch.zeros(C, device=dev, dtype=torch.float32) if has_bias else None
+        sums = torch.zeros(2 * C, device=dev, dtype=torch.float32) if has_norm else None
+        LIB.call("npfk_dwconv_bwd", _p(dy), _p(x), _p(mean), _p(var), _p(gamma), _p(beta), eps, _p(w2), _p(dh), _p(dw),
+                 _p(dbias), _p(sums), B, L, C, ks, int(relu), st)
+        dgamma = dbeta = None
+        dx = dh
+        if has_norm:
+            dgamma = torch.zeros(C, device=dev, dtype=torch.float32)
+            dbeta = torch.zeros(C, device=dev, dtype=torch.float32)
+            LIB.call("npfk_bn_bwd", _p(dh), _p(x), _p(mean), _p(var), _p(gamma), eps, _p(sums), _p(dx), _p(dgamma),
+                     _p(dbeta), B * L, C, int(training), st)
+        return (dx, dgamma, dbeta, dw.reshape(wshape), dbias, (dy if has_res else None), None, None, None, None, None,
+                None)
+
+
+def norm_act_dwconv(x, gamma, beta, w, bias, res, running_mean, running_var, training, eps, momentum, relu=True):
+    return _NormActDwConvFn.apply(x, gamma, beta, w, bias, res, running_mean, running_var, training, eps, momentum,
+                                  relu)
+
+
+class _AvgPool2Fn(Function):
+    @staticmethod
+    def forward(ctx, x):
+        require_cuda(x)
+        x = _c(x)
+        B, L, C = x.shape
+        y = torch.empty(B, L // 2, C, device=x.device, dtype=torch.float32)
+        LIB.call("npfk_avgpool2_fwd", _p(x), _p(y), B, L, C, _st())
+        ctx.shape = (B, L, C)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        B, L, C = ctx.shape
+        dy = _c(dy)
+        dx = torch.empty(B, L, C, device=dy.device, dtype=torch.float32)
+        LIB.call("npfk_avgpool2_bwd", _p(dy), _p(dx), B, L, C, _st())
+        return dx
+
+
+def avgpool2(x):
+    return _AvgPool2Fn.apply(x)
+
+
+class _Upsample2CatFn(Function):
+    """cat(upsample_linear_x2(x), skip) along channels, written straight into the concat buffer."""
+
+    @staticmethod
+    def forward(ctx, x, skip):
+        require_cuda(x, skip)
+        x = _c(x)
+        B, L, C1 = x.shape
+        st = _st()
+        if skip is None:
+            y = torch.empty(B, 2 * L, C1, device=x.device, dtype=torch.float32)
+            LIB.call("npfk_upsample2_fwd", _p(x), _p(y), C1, B, L, C1, st)
+            ctx.cfg = (B, L, C1, 0)
+            return y
+        skip = _c(skip)
+        C2 = skip.shape[-1]
+        if skip.shape[1] != 2 * L:
+            raise NpfkError(f"upsample/concat length mismatch: {2 * L} vs {skip.shape[1]}")
+        y = torch.empty(B, 2 * L, C1 + C2, device=x.device, dtype=torch.float32)
+        LIB.call("npfk_upsample2_fwd", _p(x), _p(y), C1 + C2, B, L, C1, st)
+        LIB.call("npfk_copy2d", _p(skip), C2, ctypes.c_void_p(y.data_ptr() + 4 * C1), C1 + C2, B * 2 * L, C2, st)
+        ctx.cfg = (B, L, C1, C2)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        B, L, C1, C2 = ctx.cfg
+        dy = _c(dy)
+        st = _st()
+        dx = torch.zeros(B, L, C1, device=dy.device, dtype=torch.float32)
+        LIB.call("npfk_upsample2_bwd", _p(dy), C1 + C2, _p(dx), B, L, C1, st)
+        dskip = None
+        if C2:
+            dskip = torch.empty(B, 2 * L, C2, device=dy.device, dtype=torch.float32)
+            LIB.call("npfk_copy2d", ctypes.c_void_p(dy.data_ptr() + 4 * C1), C1 + C2, _p(dskip), C2, B * 2 * L, C2, st)
+        return dx, dskip
+
+
+def upsample2_cat(x, skip=None):
+    return _Upsample2CatFn.apply(x, skip)
+
+
+# ------------------------------------------------------------------------------------------ distributions / losses
+class _LocScaleFn(Function):
+    @staticmethod
+    def forward(ctx, suff):
+        require_cuda(suff)
+        suff = _c(suff)
+        ydim = suff.shape[-1] // 2
+        n = suff.numel() // (2 * ydim)
+        loc = torch.empty(*suff.shape[:-1], ydim, device=suff.device, dtype=torch.float32)
+        scale = torch.empty_like(loc)
+        LIB.call("npfk_loc_scale_fwd", _p(suff), _p(loc), _p(scale), n, ydim, _st())
+        ctx.save_for_backward(suff)
+        return loc, scale
+
+    @staticmethod
+    def backward(ctx, dloc, dscale):
+        (suff,) = ctx.saved_tensors
+        ydim = suff.shape[-1] // 2
+        n = suff.numel() // (2 * ydim)
+        dsuff = torch.empty_like(suff)
+        LIB.call("npfk_loc_scale_bwd", _p(suff), _p(_c(dloc)), _p(_c(dscale)), _p(dsuff), n, ydim, _st())
+        return dsuff
+
+
+def loc_scale(suff):
+    """split [..., 2*ydim] into loc and scale = 0.01 + 0.99*softplus(.)"""
+    return _LocScaleFn.apply(suff)
+
+
+class _GaussNllFn(Function):
+    @staticmethod
+    def forward(ctx, suff, y):
+        # suff:[Z,B,T,2*ydim]  y:[B,T,ydim] -> sum_t log p : [Z,B]
+        require_cuda(suff, y)
+        suff, y = _c(suff), _c(y)
+        Z, B = suff.shape[0], suff.shape[1]
+        ydim = suff.shape[-1] // 2
+        T = suff.numel() // (Z * B * 2 * ydim)
+        out = torch.zeros(Z, B, device=suff.device, dtype=torch.float32)
+        LIB.call("npfk_gauss_nll_fwd", _p(suff), _p(y), _p(out), Z, B, T, ydim, _st())
+        ctx.save_for_backward(suff, y)
+        ctx.cfg = (Z, B, T, ydim)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        suff, y = ctx.saved_tensors
+        Z, B, T, ydim = ctx.cfg
+        dsuff = torch.empty_like(suff)
+        LIB.call("npfk_gauss_nll_bwd", _p(suff), _p(y), _p(_c(dout)), _p(dsuff), Z, B, T, ydim, _st())
+        return dsuff, None
+
+
+def gauss_sum_log_prob(suff, y):
+    return _GaussNllFn.apply(suff, y)
+
+
+class _LatentStatsFn(Function):
+    @staticmethod
+    def forward(ctx, suff):
+        require_cuda(suff)
+        suff = _c(suff)
+        zd = suff.shape[-1] // 2
+        n = suff.numel() // (2 * zd)
+        loc = torch.empty(*suff.shape[:-1], zd, device=suff.device, dtype=torch.float32)
+        scale = torch.empty_like(loc)
+        LIB.call("npfk_latent_stats_fwd", _p(suff), _p(loc), _p(scale), n, zd, _st())
+        ctx.save_for_backward(suff)
+        return loc, scale
+
+    @staticmethod
+    def backward(ctx, dloc, dscale):
+        (suff,) = ctx.saved_tensors
+        zd = suff.shape[-1] // 2
+        n = suff.numel() // (2 * zd)
+        dsuff = torch.empty_like(suff)
+        LIB.call("npfk_latent_stats_bwd", _p(suff), _p(_c(dloc)), _p(_c(dscale)), _p(dsuff), n, zd, _st())
+        return dsuff
+
+
+def latent_stats(suff):
+    """split [..., 2*z] into loc and scale = 0.1 + 0.9*sigmoid(.)"""
+    return _LatentStatsFn.apply(suff)
+
+
+class _RSampleFn(Function):
+    @staticmethod
+    def forward(ctx, loc, scale, eps):
+        require_cuda(loc, scale, eps)
+        loc, scale, eps = _c(loc), _c(scale), _c(eps)
+        S = eps.shape[0]
+        n = loc.numel()
+        z = torch.empty_like(eps)
+        LIB.call("npfk_rsample_fwd", _p(loc), _p(scale), _p(eps), _p(z), S, n, _st())
+        ctx.save_for_backward(eps)
+        ctx.shape = loc.shape
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        (eps,) = ctx.saved_tensors
+        S = eps.shape[0]
+        dz = _c(dz)
+        dloc = torch.empty(ctx.shape, device=dz.device, dtype=torch.float32)
+        dscale = torch.empty_like(dloc)
+        LIB.call("npfk_rsample_bwd", _p(dz), _p(eps), _p(dloc), _p(dscale), S, dloc.numel(), _st())
+        return dloc, dscale, None
+
+
+def rsample(loc, scale, eps):
+    """z[s] = loc + scale * eps[s]"""
+    return _RSampleFn.apply(loc, scale, eps)
+
+
+class _KlDiagFn(Function):
+    @staticmethod
+    def forward(ctx, lq, sq, lp, sp):
+        require_cuda(lq, sq, lp, sp)
+        lq, sq, lp, sp = _c(lq), _c(sq), _c(lp), _c(sp)
+        zd = lq.shape[-1]
+        n = lq.numel() // zd
+        kl = torch.empty(lq.shape[:-1], device=lq.device, dtype=torch.float32)
+        LIB.call("npfk_kl_diag_fwd", _p(lq), _p(sq), _p(lp), _p(sp), _p(kl), n, zd, _st())
+        ctx.save_for_backward(lq, sq, lp, sp)
+        return kl
+
+    @staticmethod
+    def backward(ctx, dkl):
+        lq, sq, lp, sp = ctx.saved_tensors
+        zd = lq.shape[-1]
+        n = lq.numel() // zd
+        outs = [torch.empty_like(lq) for _ in range(4)]
+        LIB.call("npfk_kl_diag_bwd", _p(lq), _p(sq), _p(lp), _p(sp), _p(_c(dkl)), *[_p(o) for o in outs], n, zd, _st())
+        return tuple(outs)
+
+
+def kl_diag_normal(lq, sq, lp, sp):
+    """KL(N(lq,sq) || N(lp,sp)) summed over the last dim"""
+    return _KlDiagFn.apply(lq, sq, lp, sp)
+
+
+def range_flag(x, flag, lo=-1.0, hi=1.0) -> None:
+    """flag |= any(x outside [lo,hi]); flag is a device int32 scalar tensor"""
+    require_cuda(x, flag)
+    x = _c(x.detach())
+    LIB.call("npfk_range_flag", _p(x), x.numel(), float(lo), float(hi), _p(flag), _st())
+
+
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step, grad_scale=1.0) -> None:
+    """torch.optim.Adam update on flat fp32 buffers, in place"""
+    require_cuda(param, grad, exp_avg, exp_avg_sq)
+    LIB.call("npfk_adam_step", _p(param), _p(grad), _p(exp_avg), _p(exp_avg_sq), param.numel(), float(lr), float(beta1),
+             float(beta2), float(eps), int(step), float(grad_scale), _st())
+
+
+def launch_count() -> int:
+    return LIB.launch_count()

@@ -1,0 +1,195 @@
+"""Model-level parity through the drop-in module API on cuda:0.
+
+1. against the committed golden vectors produced by the unmodified reference (tests/golden/*.pt);
+2. against the CPU oracle on fresh seeded inputs at notebook width (r_dim=128), ragged sizes, Nc=0;
+3. size-independent properties at BASELINE.json's full sizes.
+
+Gate (fp32 mode, BASELINE.json north_star): normalised max error <= 1e-4 on predictive mean / std.
+Per-target log-likelihood and loss use 1e-4 as well in this mode; parameter gradients are held to 1e-3.
+"""
+import pytest
+import torch
+
+from conftest import GOLDEN_TAGS, load_golden
+from oracle import npf_oracle as O
+from util_models import build_product, chirp_batch, perturb_, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def loss_class(tag, name):
+    import npf_gwwaveform_b200 as npf
+
+    if name in ("LNP", "AttnLNP"):
+        return npf.NLLLossLNPF if "nll" in tag else npf.ELBOLossLNPF
+    return npf.CNPFLoss
+
+
+def product_from_fixture(fix):
+    m = build_product(fix["name"], fix["r_dim"], nz=fix["n_z"], **fix["kwargs"])
+    m.load_state_dict(fix["state_dict"], strict=True)
+    m = m.cuda()
+    if "eps" in fix:
+        eps = fix["eps"].cuda()
+        m.draw_eps = lambda n, like: eps          # G4: identical latent noise on both sides
+    return m
+
+
+@pytest.mark.parametrize("tag", GOLDEN_TAGS)
+def test_golden_train_step(tag):
+    fix = load_golden(tag)
+    m = product_from_fixture(fix)
+    inp = {k: v.cuda() for k, v in fix["inputs"].items()}
+    ref = fix["train"]
+    m.train()
+    crit = loss_class(tag, fix["name"])()
+    crit.train()
+    out = m(**inp)
+    loss = crit(out, inp["Y_trgt"])
+    loss.backward()
+    p = out[0]
+    assert rel_err(p.base_dist.loc, ref["loc"]) < TOL
+    assert rel_err(p.base_dist.scale, ref["scale"]) < TOL
+    assert rel_err(p.log_prob(inp["Y_trgt"]), ref["log_prob"]) < TOL
+    assert abs(float(loss) - float(ref["loss"])) < TOL * max(1.0, abs(float(ref["loss"])))
+    if "z" in ref:
+        assert rel_err(out[1], ref["z"]) < TOL
+        assert rel_err(out[2].base_dist.scale, ref["q_zCc_scale"]) < TOL
+        assert rel_err(out[3].base_dist.loc, ref["q_zCct_loc"]) < TOL
+    grads = {k: v.grad for k, v in m.named_parameters()}
+    gmax = max(float(g.abs().max()) for g in ref["grads"].values())
+    worst = ("", 0.0)
+    for k, g in ref["grads"].items():
+        assert grads[k] is not None, k
+        err = float((grads[k].cpu() - g).abs().max()) / max(float(g.abs().max()), 1e-3 * gmax)
+        worst = max(worst, (k, err), key=lambda t: t[1])
+    assert worst[1] < 1e-3, worst
+    sd = m.state_dict()
+    for k, v in ref["state_after"].items():       # BatchNorm running statistics / counters after one step
+        assert rel_err(sd[k].float(), v.float()) < 1e-4, k
+
+
+@pytest.mark.parametrize("tag", GOLDEN_TAGS)
+def test_golden_eval(tag):
+    fix = load_golden(tag)
+    m = product_from_fixture(fix).eval()
+    inp = {k: v.cuda() for k, v in fix["inputs"].items()}
+    crit = loss_class(tag, fix["name"])(reduction=None).eval()
+    with torch.no_grad():
+        out = m(inp["X_cntxt"], inp["Y_cntxt"], inp["X_trgt"])
+        loss = crit(out, inp["Y_trgt"])
+    ref = fix["eval"]
+    assert rel_err(out[0].base_dist.loc, ref["loc"]) < TOL
+    assert rel_err(out[0].base_dist.scale, ref["scale"]) < TOL
+    assert rel_err(loss, ref["loss_per_task"]) < TOL
+
+
+ORACLE_KW = {"ConvCNP_unet": dict(unet=True, density_induced=64), "ConvCNP": dict(density_induced=64)}
+
+
+@pytest.mark.parametrize("name,B,Nc,Nt", [
+    ("CNP", 4, 64, 128), ("AttnCNP", 3, 77, 301), ("ConvCNP", 2, 50, 200), ("ConvCNP_unet", 2, 33, 129),
+    ("LNP", 2, 10, 40), ("AttnLNP", 2, 40, 150), ("AttnCNP", 2, 0, 33), ("CNP", 2, 0, 9), ("ConvCNP", 2, 0, 20),
+    ("AttnCNP", 1, 1, 1),
+])
+def test_against_oracle_notebook_width(name, B, Nc, Nt):
+    """r_dim = 128 notebook architectures, random init + perturbation, ragged sizes and empty context"""
+    torch.manual_seed(0)
+    m = build_product(name, 128, nz=3)
+    perturb_(m, 7)
+    sd = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    m = m.cuda().train()
+    inp = chirp_batch(B, max(Nc, 1), Nt, 99)
+    if Nc == 0:
+        inp["X_cntxt"], inp["Y_cntxt"] = torch.zeros(B, 0, 1), torch.zeros(B, 0, 1)
+    latent = name in ("LNP", "AttnLNP")
+    kw = dict(ORACLE_KW.get(name, {}))
+    if latent:
+        eps = torch.randn(3, B, 1, 128, generator=torch.Generator().manual_seed(5))
+        m.draw_eps = lambda n, like: eps.cuda()
+        kw.update(n_z=3, eps=eps)
+    fwd = O.FORWARDS[name.split("_")[0]]
+    args = dict(x_c=inp["X_cntxt"], y_c=inp["Y_cntxt"], x_t=inp["X_trgt"])
+    if latent:
+        args["y_t"] = inp["Y_trgt"]
+    loss_fn = O.elbo_loss if latent else O.cnpf_loss
+    ref_out, ref_loss, ref_grads = O.loss_and_grads(fwd, loss_fn, sd, args, inp["Y_trgt"], training=True, **kw)
+
+    import npf_gwwaveform_b200 as npf
+
+    crit = (npf.ELBOLossLNPF if latent else npf.CNPFLoss)().train()
+    out = m(**{k: v.cuda() for k, v in inp.items()})
+    loss = crit(out, inp["Y_trgt"].cuda())
+    loss.backward()
+    assert rel_err(out[0].base_dist.loc, ref_out["loc"]) < TOL
+    assert rel_err(out[0].base_dist.scale, ref_out["scale"]) < TOL
+    assert abs(float(loss) - float(ref_loss)) < TOL * max(1.0, abs(float(ref_loss)))
+    gmax = max(float(g.abs().max()) for g in ref_grads.values())
+    for k, p in m.named_parameters():
+        if k in ref_grads:
+            g = ref_grads[k]
+            err = float((p.grad.cpu() - g).abs().max()) / max(float(g.abs().max()), 1e-3 * gmax)
+            assert err < 1e-3, (k, err)
+
+
+def test_training_range_check_raises_value_error():
+    m = build_product("CNP", 32).cuda().train()
+    inp = {k: v.cuda() for k, v in chirp_batch(2, 5, 9, 1).items()}
+    inp["X_trgt"] = inp["X_trgt"] * 1.5
+    with pytest.raises(ValueError):
+        m(**inp)
+    m.eval()
+    m(inp["X_cntxt"], inp["Y_cntxt"], inp["X_trgt"])      # eval mode never checks (base.py:241-247)
+
+
+def test_lazy_validation_reports_one_call_late():
+    from npf_gwwaveform_b200.neuralproc import set_lazy_validation
+
+    m = build_product("CNP", 32).cuda().train()
+    inp = {k: v.cuda() for k, v in chirp_batch(2, 5, 9, 1).items()}
+    bad = dict(inp, X_trgt=inp["X_trgt"] * 1.5)
+    set_lazy_validation(True)
+    try:
+        m(**bad)
+        with pytest.raises(ValueError):
+            m(**inp)
+    finally:
+        set_lazy_validation(False)
+
+
+def test_full_size_properties_attncnp():
+    """BASELINE.json config 2 shapes (512 context / 4096 targets) on a batch slice: permutation invariance in the
+    context set, target-wise independence, and the loss equals minus the summed per-target log-likelihood."""
+    torch.manual_seed(0)
+    m = build_product("AttnCNP", 128).cuda().eval()
+    inp = {k: v.cuda() for k, v in chirp_batch(4, 512, 4096, 3).items()}
+    import npf_gwwaveform_b200 as npf
+
+    with torch.no_grad():
+        out = m(inp["X_cntxt"], inp["Y_cntxt"], inp["X_trgt"])
+        perm = torch.randperm(512, device="cuda")
+        out_p = m(inp["X_cntxt"][:, perm], inp["Y_cntxt"][:, perm], inp["X_trgt"])
+        sub = m(inp["X_cntxt"], inp["Y_cntxt"], inp["X_trgt"][:, 1000:1100])
+        crit = npf.CNPFLoss(reduction=None).eval()
+        loss = crit(out, inp["Y_trgt"])
+    loc = out[0].base_dist.loc
+    assert torch.isfinite(loc).all() and (out[0].base_dist.scale > 0.01).all()
+    assert rel_err(out_p[0].base_dist.loc, loc) < 1e-4
+    assert rel_err(sub[0].base_dist.loc, loc[:, :, 1000:1100]) < 1e-5
+    assert rel_err(loss, -out[0].log_prob(inp["Y_trgt"]).sum(-1).squeeze(0)) < 1e-5
+
+
+def test_full_size_properties_convcnp_unet():
+    """BASELINE.json config 3 shapes: translation of a whole task inside [-1,1] leaves predictions unchanged up to
+    the grid discretisation; eval-mode forward is deterministic and batch-independent."""
+    torch.manual_seed(0)
+    m = build_product("ConvCNP_unet", 128).cuda().eval()
+    inp = {k: v.cuda() for k, v in chirp_batch(3, 512, 4096, 4).items()}
+    with torch.no_grad():
+        a = m(inp["X_cntxt"], inp["Y_cntxt"], inp["X_trgt"])[0].base_dist.loc
+        b = m(inp["X_cntxt"][:1], inp["Y_cntxt"][:1], inp["X_trgt"][:1])[0].base_dist.loc
+        c = m(inp["X_cntxt"], inp["Y_cntxt"], inp["X_trgt"])[0].base_dist.loc
+    assert torch.isfinite(a).all()
+    assert rel_err(b, a[:, :1]) < 1e-5       # eval BatchNorm: tasks do not interact
+    assert torch.equal(a, c)

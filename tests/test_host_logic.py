@@ -1,0 +1,111 @@
+"""CPU-only checks of the host side: constructor wiring, state_dict layouts, error conventions, C-ABI exports."""
+import ctypes
+import json
+import os
+
+import pytest
+import torch
+
+from conftest import GOLDEN, load_golden
+from util_models import build_product
+
+
+@pytest.fixture(scope="module")
+def layouts():
+    with open(os.path.join(GOLDEN, "layouts.json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("name", ["CNP", "AttnCNP", "ConvCNP", "ConvCNP_unet", "LNP", "AttnLNP"])
+def test_param_counts_and_state_dict_layout(name, layouts):
+    # known answers: CNP.ipynb:164 (252,098), AttnCNP.ipynb:151 (252,738), ConvCNP.ipynb:164 (276,612),
+    # LNP.ipynb:149 (301,634), AttnLNP.ipynb:148 (335,170); UNet variant 1,191,556
+    m = build_product(name, 128)
+    assert sum(p.numel() for p in m.parameters()) == layouts[name]["n_params"]
+    assert {k: list(v.shape) for k, v in m.state_dict().items()} == layouts[name]["state_dict"]
+
+
+def test_known_param_counts(layouts):
+    expect = {"CNP": 252098, "AttnCNP": 252738, "ConvCNP": 276612, "LNP": 301634, "AttnLNP": 335170,
+              "ConvCNP_unet": 1191556}
+    for k, v in expect.items():
+        assert layouts[k]["n_params"] == v
+
+
+@pytest.mark.parametrize("tag", ["cnp_r32", "attncnp_r32", "convcnp_r32", "convcnp_unet_r32", "convcnp_unshared_r32",
+                                 "lnp_r32", "lnp_both_r32", "attnlnp_r32", "attncnp_pretrained", "convcnp_pretrained"])
+def test_reference_state_dicts_load_strict(tag):
+    fix = load_golden(tag)
+    m = build_product(fix["name"], fix["r_dim"], nz=fix["n_z"], **fix["kwargs"])
+    m.load_state_dict(fix["state_dict"], strict=True)
+
+
+def test_error_conventions():
+    import npf_gwwaveform_b200 as npf
+    from npf_gwwaveform_b200._lib import NpfkError
+    from npf_gwwaveform_b200.architectures import MultiheadAttender, SetConv, get_attender
+
+    with pytest.raises(ValueError):
+        npf.CNP(1, 1, encoded_path="latent")                      # base.py:134-135
+    with pytest.raises(ValueError):
+        get_attender("nonsense", 8, 8, 8)                         # attention.py:84
+    with pytest.raises(AssertionError):
+        SetConv(2, 1, 8)                                          # setcnn.py:226
+    with pytest.raises(AssertionError):
+        MultiheadAttender(12, 12, 12, n_heads=8)                  # attention.py:442-443
+    crit = npf.CNPFLoss(reduction="bogus")
+    crit.train()
+
+    class P:  # minimal stand-in distribution
+        batch_shape = (1, 2)
+
+        def log_prob(self, y):
+            return torch.zeros(1, 2, 3)
+
+    with pytest.raises(ValueError):
+        crit((P(), None, None, None), torch.zeros(2, 3, 1))       # losses.py:80-81
+    with pytest.raises(AssertionError):
+        npf.CNPFLoss().get_loss(P(), None, object(), None, torch.zeros(2, 3, 1))   # losses.py:116
+    m = build_product("CNP", 32)
+    with pytest.raises(NotImplementedError):
+        m.latent_path(None, None, None, None)                     # base.py:323-325
+    # no CPU fallback: CPU tensors are refused loudly
+    with pytest.raises(NpfkError):
+        m(torch.zeros(1, 2, 1), torch.zeros(1, 2, 1), torch.zeros(1, 3, 1))
+
+
+def test_convcnp_grid_and_extrapolation():
+    m = build_product("ConvCNP", 32, density=64)
+    assert m.n_induced == 192 and "X_induced" not in m.state_dict()          # convnp.py:104
+    torch.testing.assert_close(m.X_induced, torch.linspace(-1.5, 1.5, 192))
+    m.set_extrapolation((-1, 3))                                              # convnp.py:170-181
+    assert m.n_induced == int(64 * 5)
+
+
+def test_unet_channel_plan():
+    m = build_product("ConvCNP_unet", 128)
+    assert m.induced_to_induced.in_out_channels == [(128, 256), (256, 256), (256, 256), (512, 256), (512, 128)]
+
+
+def test_cabi_exports_every_declared_symbol():
+    from npf_gwwaveform_b200 import _lib
+
+    protos = _lib.parse_header()
+    assert len(protos) >= 35
+    assert os.path.exists(_lib.LIB_PATH), "libnpfk.so missing: run python -c 'import __graft_entry__ as g; g.build()'"
+    dll = ctypes.CDLL(_lib.LIB_PATH)
+    for name in protos:
+        assert hasattr(dll, name), f"{name} declared in include/npfk.h but not exported"
+    _lib.LIB.load()
+    assert _lib.LIB.version() >= 100
+    assert _lib.LIB.launch_count() == 0          # nothing launched without a GPU
+
+
+def test_cabi_rejects_bad_arguments_without_gpu():
+    from npf_gwwaveform_b200._lib import LIB, NpfkError
+
+    with pytest.raises(NpfkError, match="null pointer"):
+        LIB.call("npfk_linear_fwd", None, 1, None, 1, None, None, 1, 0, None, 1, 4, 4, 4, 0, 0, None)
+    with pytest.raises(NpfkError, match="head size"):
+        p = ctypes.c_void_p(16)
+        LIB.call("npfk_mha_fwd", p, p, p, p, p, 1, 4, 4, 1, 5, 1.0, None)
