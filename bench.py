@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""Headline benchmark: target-points/sec, forward + loss + backward (+ gradient all-reduce + Adam).
+
+    python bench.py --gpus N --steps K --warmup W            # product arm (CUDA kernels through the module API)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the reference algorithm (oracle port)
+
+Workload at every N: BASELINE.json configs[1] per GPU -- AttnCNP (transformer attender, r_dim 128) on synthetic
+chirp waveforms, 4096 samples, 512 context / 4096 target points, batch 256 tasks per GPU (weak scaling: the
+global batch is 256*N, sharded over ranks; the only exchange is the gradient all-reduce).  One "step" =
+forward + CNPFLoss + backward + all-reduce + Adam.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "target-points/sec fwd+bwd"
+UNIT = "target-points/s"
+WORKLOADS = {
+    # name: (model, tasks per GPU, n_context, n_target, n_z)
+    "attncnp_c2": ("AttnCNP", 256, 512, 4096, 1),
+    "convcnp_c3": ("ConvCNP_unet", 32, 512, 4096, 1),
+    "attnlnp_c4": ("AttnLNP", 16, 512, 4096, 32),
+    "cnp_c1": ("CNP", 64, 64, 128, 1),
+}
+WORKLOAD_TEXT = {
+    "attncnp_c2": "BASELINE.json configs[1]: AttnCNP (transformer attender, r_dim=128) on synthetic 1D chirp waveforms, "
+                  "4096 samples, 512 context / 4096 target points, batch 256 tasks per GPU, training step",
+    "convcnp_c3": "BASELINE.json configs[2]: ConvCNP 1D (SetConv + UNet, density 64) on chirps, 512/4096, 32 tasks per GPU",
+    "attnlnp_c4": "BASELINE.json configs[3]: AttnLNP, 32 z-samples, ELBO, 512/4096, 16 tasks per GPU",
+    "cnp_c1": "BASELINE.json configs[0]: CNP, batch 64, 64 context / 128 target",
+}
+# algorithmic forward FLOPs per target point; backward = 2x
+FLOPS_FWD_PER_TARGET = {"attncnp_c2": 616.2e3, "convcnp_c3": 280.7e3, "attnlnp_c4": 8.93e6, "cnp_c1": 316.8e3}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="attncnp_c2", choices=list(WORKLOADS))
+    ap.add_argument("--mode", default=os.environ.get("NPFK_MODE", "fp32"), choices=["fp32", "fast"])
+    ap.add_argument("--tasks-per-gpu", type=int, default=0, help="override the per-GPU batch (debugging only)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(hbm_gbs=p["hbm_gbs"], tflops=p["bf16_tflops_sustained"], source="measured (MEASURED_PEAKS.json, sustained)")
+    return dict(hbm_gbs=6650.0, tflops=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+# ------------------------------------------------------------------------------------------ CPU arm / cpu_baseline
+def cpu_reference_rate(workload, seconds, warmup=1, min_iters=2, max_iters=50, chunk=None):
+    """Times the reference algorithm (oracle port, torch CPU fp32, all host threads) on a bounded chunk of the
+    workload: forward + loss + backward.  Returns (target-points/s, description, cores, ms per chunk)."""
+    import torch
+
+    from oracle import npf_oracle as O
+    from util_models import build_product, chirp_batch
+
+    model, B, Nc, Nt, nz = WORKLOADS[workload]
+    chunk = chunk or {"attncnp_c2": 4, "convcnp_c3": 2, "attnlnp_c4": 1, "cnp_c1": 64}[workload]
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    sd = {k: v.detach().clone() for k, v in build_product(model, 128, nz=nz).state_dict().items()}
+    inp = chirp_batch(chunk, Nc, Nt, 1234)
+    args = dict(x_c=inp["X_cntxt"], y_c=inp["Y_cntxt"], x_t=inp["X_trgt"])
+    kw = {}
+    fwd = O.FORWARDS[model.split("_")[0]]
+    loss_fn = O.cnpf_loss
+    if model.startswith("ConvCNP"):
+        kw = dict(unet=model.endswith("unet"), density_induced=64)
+    if "LNP" in model:
+        args["y_t"] = inp["Y_trgt"]
+        kw = dict(n_z=nz)
+        loss_fn = O.elbo_loss
+
+    def one():
+        O.loss_and_grads(fwd, loss_fn, sd, args, inp["Y_trgt"], training=True, **kw)
+
+    for _ in range(warmup):
+        one()
+    times = []
+    t_end = time.time() + seconds
+    while (len(times) < min_iters or time.time() < t_end) and len(times) < max_iters:
+        t0 = time.time()
+        one()
+        times.append(time.time() - t0)
+    t = statistics.median(times)
+    desc = (f"{chunk}-task chunk of the workload ({Nc} context / {Nt} target, n_z={nz}), forward+loss+backward, "
+            f"median of {len(times)} runs after {warmup} warm-up, torch {torch.__version__} CPU fp32, {threads} threads")
+    return chunk * Nt / t, desc, threads, t * 1e3
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_iters = max(args.steps, 1)
+    rate, desc, cores, ms = cpu_reference_rate(args.workload, seconds=1e9, warmup=max(args.warmup, 1), min_iters=n_iters,
+                                               max_iters=n_iters)
+    model, B, Nc, Nt, nz = WORKLOADS[args.workload]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD_TEXT[args.workload], "sample": desc, "timing": "host wall clock"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference = unmodified algorithm of MarinerQ/npf_GWwaveform restated in oracle/npf_oracle.py (the Python "
+                "reference itself cannot travel to the GPU box); runs on host cores only",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, f"/tmp/npf_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        with open(self.path) as f:
+            for ln in f:
+                parts = [p.strip() for p in ln.split(",")]
+                if len(parts) < 9:
+                    continue
+                try:
+                    sm.append(float(parts[1]))
+                    mx.append(float(parts[2]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, parts[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------ product arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import npf_gwwaveform_b200 as npf
+    from npf_gwwaveform_b200 import kernels as Kn
+    from npf_gwwaveform_b200.neuralproc import set_lazy_validation
+    from npf_gwwaveform_b200.training import FlatAdamTrainer
+    from util_models import build_product, chirp_batch
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (product arm) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    model_name, B, Nc, Nt, nz = WORKLOADS[args.workload]
+    if args.tasks_per_gpu:
+        B = args.tasks_per_gpu
+    npf.set_mode(args.mode)
+    set_lazy_validation(True)                       # range flag still computed every step, read one step late
+    torch.manual_seed(0)                            # identical initial weights on every rank
+    model = build_product(model_name, 128, nz=nz).to(dev).train()
+    crit = (npf.ELBOLossLNPF if "LNP" in model_name else npf.CNPFLoss)().train()
+    trainer = FlatAdamTrainer(model, crit, lr=1e-3)
+
+    # per-rank synthetic shard (seed 1234 + rank), resident in HBM for `value`, pinned on the host for `e2e`
+    host = {k: v.pin_memory() for k, v in chirp_batch(B, Nc, Nt, 1234 + rank).items()}
+    resident = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_loop(step_fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            step_fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    def step_resident():
+        return trainer.step(resident)
+
+    loss_host = torch.zeros(1).pin_memory()
+
+    def step_e2e():
+        batch = {k: v.to(dev, non_blocking=True) for k, v in host.items()}      # H2D of this step's inputs
+        loss = trainer.step(batch)
+        loss_host.copy_(loss.reshape(1), non_blocking=False)                    # D2H read of the step's result
+        return loss_host
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    timed_names = ["npfk_linear_fwd", "npfk_linear_bwd_dx", "npfk_linear_bwd_dw", "npfk_mha_fwd", "npfk_mha_bwd"]
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    n0 = Kn.launch_count()
+    with Kn.KernelTimer(timed_names) as kt:
+        total_ms = timed_loop(step_resident, args.steps)
+    launches = Kn.launch_count() - n0
+    clocks = sampler.stop() if rank == 0 else {}
+    ksum = kt.summary()
+    ms_per_step = total_ms / args.steps
+    value = world * B * Nt / (ms_per_step * 1e-3)
+
+    for _ in range(2):
+        step_e2e()
+    e2e_ms = timed_loop(step_e2e, args.steps) / args.steps
+    e2e_value = world * B * Nt / (e2e_ms * 1e-3)
+    final_loss = float(step_resident().item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    pk = peaks()
+    # dominant kernel family = the one with the largest share of the step
+    fam = {"sgemm (npfk_linear_fwd/bwd_dx/bwd_dw)": ["npfk_linear_fwd", "npfk_linear_bwd_dx", "npfk_linear_bwd_dw"],
+           "mha (npfk_mha_fwd/bwd)": ["npfk_mha_fwd", "npfk_mha_bwd"]}
+    fam_ms = {f: sum(ksum.get(n, {}).get("ms_total", 0.0) for n in ns) for f, ns in fam.items()}
+    dom = max(fam_ms, key=fam_ms.get)
+    dom_work = sum(ksum.get(n, {}).get("work_total", 0.0) for n in fam[dom])
+    dom_calls = sum(ksum.get(n, {}).get("calls", 0) for n in fam[dom])
+    achieved = dom_work / (fam_ms[dom] * 1e-3) / 1e12 if fam_ms[dom] > 0 else 0.0
+    roofline = {
+        "bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s",
+        "frac": achieved / pk["tflops"], "traffic": None, "peak_source": pk["source"],
+        "launches_timed": dom_calls, "avg_launch_ms": fam_ms[dom] / max(dom_calls, 1),
+        "share_of_step": fam_ms[dom] / total_ms,
+        "flops_per_launch": dom_work / max(dom_calls, 1),
+        "whole_step": {"algorithmic_tflops": 3 * FLOPS_FWD_PER_TARGET[args.workload] * B * Nt / (ms_per_step * 1e-3) / 1e12,
+                       "frac_of_peak": 3 * FLOPS_FWD_PER_TARGET[args.workload] * B * Nt / (ms_per_step * 1e-3) / 1e12 / pk["tflops"]},
+        "other_kernels_ms_per_step": {f: fam_ms[f] / args.steps for f in fam},
+    }
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.mode == "fp32" else "f16 operands (11-bit mantissa, tf32-equivalent), f32 accumulate",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD_TEXT[args.workload], "tasks_per_gpu": B, "global_batch": B * world,
+                   "n_context": Nc, "n_target": Nt, "n_z": nz, "mode": args.mode,
+                   "step": "forward + loss + backward + gradient all-reduce + Adam",
+                   "parallelism": f"data-parallel over tasks x{world}",
+                   "l2": "activations streamed per step (several GB) exceed the 126 MB L2; no explicit flush"},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d_bytes * world,
+                "d2h_bytes_per_step": 4 * world,
+                "path": "pinned host tensors -> .to(device) -> model(**batch) -> criterion -> backward -> Adam -> loss to host"},
+        "gpu_launches": launches,
+        "roofline": roofline,
+        "final_loss": final_loss,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        rate, desc, cores, _ = cpu_reference_rate(args.workload, seconds=args.cpu_seconds)
+        line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -607,3 +607,59 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step, gra
 
 def launch_count() -> int:
     return LIB.launch_count()
+
+
+# ------------------------------------------------------------------------------------------ per-kernel timing (bench.py)
+class KernelTimer:
+    """Brackets selected C-ABI calls with CUDA events on the launching stream (torch's current stream) and
+    accumulates algorithmic work per call.  Used by bench.py for the roofline of the dominant kernel."""
+
+    def __init__(self, names):
+        self.names = set(names)
+        self.records = []          # (name, work, ev0, ev1)
+        self._orig = None
+
+    def _work(self, name, a):
+        # argument positions follow include/npfk.h
+        if name == "npfk_linear_fwd":
+            return 2.0 * a[10] * a[11] * a[12]
+        if name in ("npfk_linear_bwd_dx", "npfk_linear_bwd_dw"):
+            M, N, Kd = (a[6], a[7], a[8]) if name == "npfk_linear_bwd_dx" else (a[7], a[8], a[9])
+            return 2.0 * M * N * Kd
+        if name == "npfk_mha_fwd":
+            B, Nq, Nk, H, D = a[5:10]
+            return 4.0 * B * H * Nq * Nk * D
+        if name == "npfk_mha_bwd":
+            B, Nq, Nk, H, D = a[10:15]
+            return 14.0 * B * H * Nq * Nk * D      # dq pass: s, dp, dq (6) ; dkv pass: s, dp, dv, dk (8)
+        return 0.0
+
+    def __enter__(self):
+        self._orig = LIB.call
+
+        def timed(name, *args):
+            if name not in self.names:
+                return self._orig(name, *args)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            self._orig(name, *args)
+            e1.record()
+            self.records.append((name, self._work(name, args), e0, e1))
+
+        LIB.call = timed
+        return self
+
+    def __exit__(self, *exc):
+        LIB.call = self._orig
+
+    def summary(self):
+        """{name: dict(calls, ms_total, ms_avg, work_total)} -- call after torch.cuda.synchronize()"""
+        out = {}
+        for name, work, e0, e1 in self.records:
+            d = out.setdefault(name, dict(calls=0, ms_total=0.0, work_total=0.0))
+            d["calls"] += 1
+            d["ms_total"] += e0.elapsed_time(e1)
+            d["work_total"] += work
+        for d in out.values():
+            d["ms_avg"] = d["ms_total"] / max(d["calls"], 1)
+        return out

@@ -1,0 +1,161 @@
+"""Data-parallel training step over task batches (one process per GPU, torch.distributed / NCCL).
+
+The reference trains through skorch on one device (utils/train.py:243-263: Adam, lr 1e-3) and has no distributed
+code.  Tasks are independent, so the batch is sharded across ranks; the only exchange per step is the
+gradient all-reduce.  Design:
+
+* all parameters live in ONE flat fp32 buffer (views), all gradients in one flat buffer, laid out in the order
+  in which backward finishes them (measured on a calibration step);
+* the flat gradient is cut into a few buckets; a bucket's NCCL all-reduce is issued from the
+  post-accumulate-grad hook of its last parameter, so it travels over NVLink while backward is still running;
+* Adam runs as one npfk kernel over the flat buffers after the last bucket has landed.
+
+With world_size == 1 the same code runs without any collective.  BatchNorm statistics stay per replica
+(SURVEY.md 8e default).
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import kernels as K
+
+__all__ = ["FlatAdamTrainer", "shard_range"]
+
+
+def shard_range(n_items: int, rank: int, world: int):
+    """Contiguous, balanced [lo, hi) slice of ``n_items`` independent tasks for ``rank`` (no communication)."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class FlatAdamTrainer:
+    """forward -> loss -> backward (with overlapped gradient all-reduce) -> Adam, on flat buffers."""
+
+    def __init__(self, model: torch.nn.Module, criterion: Callable, lr: float = 1e-3, betas=(0.9, 0.999),
+                 eps: float = 1e-8, n_buckets: int = 2, process_group=None, adam_impl: Optional[Callable] = None,
+                 overlap: bool = True):
+        self.model, self.criterion = model, criterion
+        self.lr, self.betas, self.eps = lr, betas, eps
+        self.group = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        self.n_buckets = max(1, n_buckets)
+        self.overlap = overlap and self.world > 1
+        self.adam_impl = adam_impl or K.adam_step
+        self.step_count = 0
+        self.params: List[torch.nn.Parameter] = [p for p in model.parameters() if p.requires_grad]
+        self._order: Optional[List[int]] = None          # readiness order measured on the first step
+        self._fired: List[int] = []
+        self._pending = []
+        self._hooks = []
+        self._build_flat(list(range(len(self.params))))
+        self._install_hooks()
+
+    # ------------------------------------------------------------------ flat storage
+    def _build_flat(self, order: List[int]) -> None:
+        dev = self.params[0].device
+        total = sum(p.numel() for p in self.params)
+        flat_p = torch.empty(total, device=dev, dtype=torch.float32)
+        flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
+        old_m = getattr(self, "exp_avg", None)
+        self.offsets = {}
+        off = 0
+        with torch.no_grad():
+            for i in order:
+                p = self.params[i]
+                n = p.numel()
+                flat_p[off:off + n].copy_(p.detach().reshape(-1))
+                p.data = flat_p[off:off + n].view_as(p)
+                p.grad = flat_g[off:off + n].view_as(p)
+                self.offsets[i] = (off, n)
+                off += n
+        self.flat_param, self.flat_grad = flat_p, flat_g
+        if old_m is None:
+            self.exp_avg = torch.zeros_like(flat_p)
+            self.exp_avg_sq = torch.zeros_like(flat_p)
+        # bucket boundaries: equal element counts, cut at parameter boundaries, in layout (= readiness) order
+        self.bucket_of = {}
+        self.bucket_slices = []
+        target = total / self.n_buckets
+        start, b = 0, 0
+        for i in order:
+            o, n = self.offsets[i]
+            self.bucket_of[i] = b
+            if (o + n) >= target * (b + 1) and b < self.n_buckets - 1:
+                self.bucket_slices.append((start, o + n))
+                start, b = o + n, b + 1
+        self.bucket_slices.append((start, total))
+        self.bucket_last = {}
+        for i in order:                                   # last parameter (in readiness order) of each bucket
+            self.bucket_last[self.bucket_of[i]] = i
+        self.layout_order = order
+
+    def _install_hooks(self) -> None:
+        for i, p in enumerate(self.params):
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
+
+    def _make_hook(self, i: int):
+        def hook(_param):
+            self._fired.append(i)
+            if self.overlap and self._order is not None and self.bucket_last.get(self.bucket_of[i]) == i:
+                self._launch_bucket(self.bucket_of[i])
+        return hook
+
+    def _launch_bucket(self, b: int) -> None:
+        lo, hi = self.bucket_slices[b]
+        if hi > lo:
+            self._pending.append(dist.all_reduce(self.flat_grad[lo:hi], op=dist.ReduceOp.SUM, group=self.group,
+                                                 async_op=True))
+
+    # ------------------------------------------------------------------ one optimisation step
+    def step(self, batch: dict) -> torch.Tensor:
+        """``batch`` holds X_cntxt, Y_cntxt, X_trgt, Y_trgt of this rank's shard; returns the local loss (device)."""
+        self.flat_grad.zero_()
+        self._fired.clear()
+        self._pending.clear()
+        out = self.model(**batch)
+        loss = self.criterion(out, batch["Y_trgt"])
+        loss.backward()
+        for p_idx, p in enumerate(self.params):          # autograd may have replaced a .grad view (it must not)
+            o, n = self.offsets[p_idx]
+            if p.grad is None or p.grad.data_ptr() != self.flat_grad.data_ptr() + 4 * o:
+                if p.grad is not None:
+                    self.flat_grad[o:o + n].copy_(p.grad.reshape(-1))
+                p.grad = self.flat_grad[o:o + n].view_as(p)
+        if self.world > 1:
+            if self.overlap and self._order is not None:
+                for w in self._pending:
+                    w.wait()
+            else:
+                dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+        self.step_count += 1
+        self.adam_impl(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0],
+                       self.betas[1], self.eps, self.step_count, 1.0 / self.world)
+        if self._order is None:                           # calibration: re-lay the buffers in readiness order
+            seen, order = set(), []
+            for i in self._fired:
+                if i not in seen:
+                    seen.add(i)
+                    order.append(i)
+            order += [i for i in range(len(self.params)) if i not in seen]
+            self._order = order
+            m, v = self._gather_state(self.exp_avg), self._gather_state(self.exp_avg_sq)
+            self._build_flat(order)
+            self._scatter_state(self.exp_avg, m)
+            self._scatter_state(self.exp_avg_sq, v)
+        return loss.detach()
+
+    def _gather_state(self, flat):
+        return {i: flat[o:o + n].clone() for i, (o, n) in self.offsets.items()}
+
+    def _scatter_state(self, flat, parts):
+        for i, (o, n) in self.offsets.items():
+            flat[o:o + n].copy_(parts[i])
+
+    def close(self) -> None:
+        for h in self._hooks:
+            h.remove()
+        self._hooks.clear()

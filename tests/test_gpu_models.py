@@ -114,7 +114,9 @@ def test_against_oracle_notebook_width(name, B, Nc, Nt):
     if latent:
         args["y_t"] = inp["Y_trgt"]
     loss_fn = O.elbo_loss if latent else O.cnpf_loss
-    ref_out, ref_loss, ref_grads = O.loss_and_grads(fwd, loss_fn, sd, args, inp["Y_trgt"], training=True, **kw)
+    # fp64 oracle: removes the reference side's own fp32 noise from the gradient comparison
+    ref_out, ref_loss, ref_grads = O.loss_and_grads(fwd, loss_fn, sd, args, inp["Y_trgt"], dtype=torch.float64,
+                                                    training=True, **kw)
 
     import npf_gwwaveform_b200 as npf
 
@@ -129,7 +131,7 @@ def test_against_oracle_notebook_width(name, B, Nc, Nt):
     for k, p in m.named_parameters():
         if k in ref_grads:
             g = ref_grads[k]
-            err = float((p.grad.cpu() - g).abs().max()) / max(float(g.abs().max()), 1e-3 * gmax)
+            err = float((p.grad.cpu().double() - g).abs().max()) / max(float(g.abs().max()), 1e-3 * gmax)
             assert err < 1e-3, (k, err)
 
 

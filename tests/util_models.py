@@ -65,7 +65,8 @@ def chirp_batch(B, Nc, Nt, seed, device="cpu"):
     k = 20 + 60 * torch.rand(B, 1, 1, generator=g)
     ph = 2 * math.pi * torch.rand(B, 1, 1, generator=g)
     y = (0.1 + tau) ** 2 * torch.sin(2 * math.pi * (f0 * tau + 0.5 * k * tau ** 2) + ph)
-    y = (y - y.mean(1, keepdim=True)) / y.std(1, keepdim=True)
+    if Nt > 1:
+        y = (y - y.mean(1, keepdim=True)) / y.std(1, keepdim=True)
     idx = torch.stack([torch.randperm(Nt, generator=g)[:Nc] for _ in range(B)]).unsqueeze(-1)
     out = dict(X_cntxt=x.gather(1, idx), Y_cntxt=y.gather(1, idx), X_trgt=x, Y_trgt=y)
     return {k_: v.to(device) for k_, v in out.items()}
