@@ -257,9 +257,13 @@ setconv_bwd_kernel(const SetConvArgs a, const float* __restrict__ out, const flo
                         const float inp1 = rbf_inp(s.Xk[j], xq, sigma_d, a.p);
                         dsig1 += (dD * expf(inp1)) * (-a.p * inp1 / sigma_d);
                     } else {
+                        // d inp = softmax part + density part.  The softmax part sums to zero over keys, so its
+                        // contribution sum_k ds_k*inp_k equals sum_k ds_k*(inp_k - m): same value, no cancellation
+                        // between terms of magnitude |m| (far queries have |m| ~ 1e4).
                         const float e = expf(inp - m);
-                        const float dinp = e * inv_l * (dp[i] - dot) + ddens * e * emax;
-                        dsig0 += dinp * (-a.p * inp / sigma);
+                        const float ds = e * inv_l * (dp[i] - dot);
+                        const float dd = ddens * e * emax;
+                        dsig0 += (ds * (inp - m) + dd * inp) * (-a.p / sigma);
                     }
                 }
             }
