@@ -27,7 +27,7 @@ extern "C" {
 #define NPFK_ERR_CUDA (-3)        /* CUDA runtime error at launch */
 
 #define NPFK_MODE_FP32 0 /* fp32 FFMA arithmetic: the <=1e-4 parity mode */
-#define NPFK_MODE_FAST 1 /* tcgen05 tensor-core arithmetic (fp16 operands = tf32-width mantissa, fp32 accumulate) */
+#define NPFK_MODE_FAST 1 /* tcgen05 tensor-core arithmetic: tf32 operands read from the fp32 tensors, fp32 accumulate in TMEM */
 
 /* ---- library ---------------------------------------------------------------------------- */
 int npfk_version(void);
@@ -50,12 +50,17 @@ int npfk_linear_fwd(const float* x, int64_t ldx, const float* w, int64_t ldw, co
 /* g[m,n] = dy[m,n] * (y[m,n] > 0)  (ReLU backward; g may alias dy) */
 int npfk_relu_bwd(const float* dy, int64_t lddy, const float* y, int64_t ldy, float* g, int64_t ldg,
                   int64_t M, int N, void* stream);
-/* dx[m,k] = sum_n g[m,n] w[n,k] */
-int npfk_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw, float* dx, int64_t lddx,
-                       int64_t M, int N, int K, int mode, void* stream);
+/* dx[m,k] = (mask == NULL || mask[m,k] > 0) ? sum_n g[m,n] w[n,k] : 0
+ * mask = saved output of the ReLU layer below: its backward is fused into this epilogue. */
+int npfk_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw, const float* mask, int64_t ldmask,
+                       float* dx, int64_t lddx, int64_t M, int N, int K, int mode, void* stream);
 /* dw[n,k] += sum_m g[m,n] x[m,k] ; db[n] += sum_m g[m,n]  (db may be NULL) */
 int npfk_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx, float* dw, int64_t lddw,
                        float* db, int64_t M, int N, int K, int mode, void* stream);
+/* dst[i] = round-to-nearest tf32(src[i]) (weights, before they meet tcgen05.mma.kind::tf32 which truncates) */
+int npfk_round_tf32(const float* src, float* dst, int64_t n, void* stream);
+/* != 0 when a tcgen05 kernel gave up on a bounded mbarrier wait since the last call (synchronises; tests only) */
+int npfk_tc_abort_code(void);
 /* out[r, n] = sum_{j} g[(j*rows + r), n] for j < reps  (gradient of a row-broadcast residual / bias) */
 int npfk_rows_fold_sum(const float* g, int64_t ldg, float* out, int64_t ldo, int64_t rows, int64_t reps, int N,
                        void* stream);

@@ -17,6 +17,7 @@ struct GemmArgs {
     int64_t I; int J; int64_t R;            // output rows / cols, reduction length
     const float* bias;                      // [J] or null
     const float* res; int64_t ldres, res_rows;
+    const float* mask; int64_t ldmask;      // output zeroed where mask(i, j) <= 0 (ReLU backward of the layer below)
     int relu; int atomic;
     int64_t r_chunk;                        // reduction elements handled per blockIdx.z
 };
@@ -145,6 +146,7 @@ sgemm_kernel(const GemmArgs p) {
                 if (p.bias) v += __ldg(p.bias + gj);
                 if (p.res) v += __ldg(p.res + (gi % res_rows) * p.ldres + gj);
                 if (p.relu) v = fmaxf(v, 0.f);
+                if (p.mask && !(__ldg(p.mask + gi * p.ldmask + gj) > 0.f)) v = 0.f;
                 p.C[gi * p.ldc + gj] = v;
             }
         }
@@ -231,6 +233,28 @@ inline unsigned grid_for(int64_t total, int block, int max_blocks = kNumSMs * 16
     return (unsigned)b;
 }
 
+// tc_gemm.cu: tcgen05 kernels for NPFK_MODE_FAST
+namespace tc {
+bool nt_eligible(const float* a, int64_t lda, const float* b, int64_t ldb, const float* c, int64_t ldc, int64_t M, int N,
+                 int K, const float* res, int64_t ldres, const float* mask, int64_t ldmask);
+bool tn_eligible(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t M, int N, int K);
+int tc_linear_fwd(const float* x, int64_t ldx, const float* w, int64_t ldw, const float* bias, const float* res,
+                  int64_t ldres, int64_t res_rows, float* y, int64_t ldy, int64_t M, int N, int K, int relu,
+                  int round_out, cudaStream_t st);
+int tc_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw, const float* mask, int64_t ldmask,
+                     float* dx, int64_t lddx, int64_t M, int N, int K, cudaStream_t st);
+int tc_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx, float* dw, int64_t lddw, float* db,
+                     int64_t M, int N, int K, cudaStream_t st);
+}  // namespace tc
+
+__global__ void round_tf32_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t n) {
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t r;
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(src[e]));
+        dst[e] = __uint_as_float(r);
+    }
+}
+
 }  // namespace npfk
 
 using namespace npfk;
@@ -243,7 +267,10 @@ int npfk_linear_fwd(const float* x, int64_t ldx, const float* w, int64_t ldw, co
     NPFK_REQUIRE(x && w && y, "linear_fwd: null pointer");
     NPFK_REQUIRE(M >= 0 && N > 0 && K > 0, "linear_fwd: bad shape M=%lld N=%d K=%d", (long long)M, N, K);
     NPFK_REQUIRE(ldx >= K && ldw >= K && ldy >= N, "linear_fwd: leading dimension too small");
-    NPFK_REQUIRE(mode == NPFK_MODE_FP32, "linear_fwd: mode %d is served by npfk_mlp_* entry points", mode);
+    NPFK_REQUIRE(mode == NPFK_MODE_FP32 || mode == NPFK_MODE_FAST, "linear_fwd: unknown mode %d", mode);
+    if (mode == NPFK_MODE_FAST && tc::nt_eligible(x, ldx, w, ldw, y, ldy, M, N, K, res, ldres, nullptr, 0))
+        return tc::tc_linear_fwd(x, ldx, w, ldw, bias, res, ldres, res_rows, y, ldy, M, N, K, relu, /*round_out=*/relu,
+                                 as_stream(stream));
     GemmArgs a{};
     a.A = x; a.a_row = ldx; a.a_red = 1;
     a.B = w; a.b_red = 1; a.b_col = ldw;
@@ -262,11 +289,14 @@ int npfk_relu_bwd(const float* dy, int64_t lddy, const float* y, int64_t ldy, fl
     return check_launch("relu_bwd");
 }
 
-int npfk_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw, float* dx, int64_t lddx, int64_t M,
-                       int N, int K, int mode, void* stream) {
+int npfk_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw, const float* mask, int64_t ldmask,
+                       float* dx, int64_t lddx, int64_t M, int N, int K, int mode, void* stream) {
     NPFK_REQUIRE(g && w && dx, "linear_bwd_dx: null pointer");
-    NPFK_REQUIRE(mode == NPFK_MODE_FP32, "linear_bwd_dx: unsupported mode %d", mode);
+    NPFK_REQUIRE(mode == NPFK_MODE_FP32 || mode == NPFK_MODE_FAST, "linear_bwd_dx: unknown mode %d", mode);
+    if (mode == NPFK_MODE_FAST && tc::nt_eligible(g, ldg, w, ldw, dx, lddx, M, K, N, nullptr, 0, mask, ldmask))
+        return tc::tc_linear_bwd_dx(g, ldg, w, ldw, mask, ldmask, dx, lddx, M, N, K, as_stream(stream));
     GemmArgs a{};
+    a.mask = mask; a.ldmask = ldmask;
     a.A = g; a.a_row = ldg; a.a_red = 1;
     a.B = w; a.b_red = ldw; a.b_col = 1;
     a.C = dx; a.ldc = lddx;
@@ -277,8 +307,10 @@ int npfk_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw,
 int npfk_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx, float* dw, int64_t lddw, float* db,
                        int64_t M, int N, int K, int mode, void* stream) {
     NPFK_REQUIRE(g && x && dw, "linear_bwd_dw: null pointer");
-    NPFK_REQUIRE(mode == NPFK_MODE_FP32, "linear_bwd_dw: unsupported mode %d", mode);
+    NPFK_REQUIRE(mode == NPFK_MODE_FP32 || mode == NPFK_MODE_FAST, "linear_bwd_dw: unknown mode %d", mode);
     if (M <= 0) return NPFK_OK;
+    if (mode == NPFK_MODE_FAST && tc::tn_eligible(g, ldg, x, ldx, M, N, K))
+        return tc::tc_linear_bwd_dw(g, ldg, x, ldx, dw, lddw, db, M, N, K, as_stream(stream));
     GemmArgs a{};
     a.A = g; a.a_row = 1; a.a_red = ldg;
     a.B = x; a.b_red = ldx; a.b_col = 1;
@@ -292,6 +324,13 @@ int npfk_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx,
         rc = check_launch("colsum");
     }
     return rc;
+}
+
+int npfk_round_tf32(const float* src, float* dst, int64_t n, void* stream) {
+    NPFK_REQUIRE(src && dst, "round_tf32: null pointer");
+    if (n == 0) return NPFK_OK;
+    NPFK_LAUNCH(round_tf32_kernel, grid_for(n, 256), 256, 0, as_stream(stream), src, dst, n);
+    return check_launch("round_tf32");
 }
 
 int npfk_rows_fold_sum(const float* g, int64_t ldg, float* out, int64_t ldo, int64_t rows, int64_t reps, int N,

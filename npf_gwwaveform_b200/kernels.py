@@ -83,6 +83,32 @@ def _weight_view(w: torch.Tensor):
 
 
 # ------------------------------------------------------------------------------------------ Linear
+_tf32_cache = {}
+
+
+def tf32_weight(w: torch.Tensor) -> torch.Tensor:
+    """Round-to-nearest tf32 copy of a weight (tcgen05.mma.kind::tf32 truncates its fp32 operands).
+
+    Cached per (storage, version) outside CUDA-graph capture; inside a capture the rounding kernel is
+    always recorded so that replays see the current weights."""
+    wv, _ = _weight_view(w.detach())
+    if not wv.is_contiguous():
+        wv = wv.contiguous()
+    capturing = torch.cuda.is_current_stream_capturing()
+    key = (w.data_ptr(), tuple(w.shape))
+    if not capturing:
+        hit = _tf32_cache.get(key)
+        if hit is not None and hit[0] == w._version:
+            return hit[1]
+    out = torch.empty_like(wv)
+    LIB.call("npfk_round_tf32", _p(wv), _p(out), wv.numel(), _st())
+    if not capturing:
+        if len(_tf32_cache) > 4096:
+            _tf32_cache.clear()
+        _tf32_cache[key] = (w._version, out)
+    return out
+
+
 class _LinearFn(Function):
     @staticmethod
     def forward(ctx, x, w, b, res, relu: bool):
@@ -90,7 +116,12 @@ class _LinearFn(Function):
         N, K = w.shape
         lead = x.shape[:-1]
         xv, ldx = _rows_view(x)
-        wv, ldw = _weight_view(w)
+        mode = _state["mode"]
+        if mode == MODE_FAST:
+            wv = tf32_weight(w)
+            ldw = wv.shape[1]
+        else:
+            wv, ldw = _weight_view(w)
         M = 1
         for s in lead:
             M *= s
@@ -104,8 +135,9 @@ class _LinearFn(Function):
         y = torch.empty(*lead, N, device=x.device, dtype=torch.float32)
         if M > 0:
             LIB.call("npfk_linear_fwd", _p(xv), ldx, _p(wv), ldw, _p(bv), _p(resv), N, res_rows, _p(y), N, M, N, K,
-                     int(relu), MODE_FP32, _st())
+                     int(relu), mode, _st())
         ctx.relu = relu
+        ctx.mode = mode
         ctx.dims = (M, N, K, ldx, ldw, res_rows)
         ctx.has_b = b is not None
         ctx.has_res = res is not None
@@ -128,14 +160,14 @@ class _LinearFn(Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty(*dy.shape[:-1], K, device=dy.device, dtype=torch.float32)
             if M > 0:
-                LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wv), ldw, _p(dx), K, M, N, K, MODE_FP32, st)
+                LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wv), ldw, None, 0, _p(dx), K, M, N, K, ctx.mode, st)
         need_w = ctx.needs_input_grad[1]
         need_b = ctx.has_b and ctx.needs_input_grad[2]
         if need_w or need_b:
             dw = torch.zeros(N, K, device=dy.device, dtype=torch.float32)
             db = torch.zeros(N, device=dy.device, dtype=torch.float32) if need_b else None
             if M > 0:
-                LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(xv), ldx, _p(dw), K, _p(db), M, N, K, MODE_FP32, st)
+                LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(xv), ldx, _p(dw), K, _p(db), M, N, K, ctx.mode, st)
         if ctx.has_res and ctx.needs_input_grad[3]:
             if res_rows == M:
                 dres = g.reshape(ctx.res_shape)
@@ -624,7 +656,7 @@ class KernelTimer:
         if name == "npfk_linear_fwd":
             return 2.0 * a[10] * a[11] * a[12]
         if name in ("npfk_linear_bwd_dx", "npfk_linear_bwd_dw"):
-            M, N, Kd = (a[6], a[7], a[8]) if name == "npfk_linear_bwd_dx" else (a[7], a[8], a[9])
+            M, N, Kd = (a[8], a[9], a[10]) if name == "npfk_linear_bwd_dx" else (a[7], a[8], a[9])
             return 2.0 * M * N * Kd
         if name == "npfk_mha_fwd":
             B, Nq, Nk, H, D = a[5:10]

@@ -1,0 +1,86 @@
+"""NPFK_MODE_FAST (tcgen05 tf32 tensor-core kernels) against float64 references.
+
+Tolerances: tf32 operands carry a 10-bit mantissa (unit round-off 2^-11 = 4.9e-4), accumulation is fp32 in
+TMEM, so a K-term dot product is good to about 1e-3 of the output scale; the gates below are normalised max
+errors  max|a-b| / max|b|  <= 2e-3 for single kernels (BASELINE.json north_star: <=1e-3 relative on the
+per-target log-likelihood in bf16/TF32 mode is checked on the models in test_gpu_models_fast).
+"""
+import math
+
+import pytest
+import torch
+
+from util_models import rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-3
+
+
+@pytest.fixture(autouse=True)
+def fast_mode():
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    Kn.set_mode("fast")
+    yield
+    Kn.set_mode("fp32")
+    torch.cuda.synchronize()
+    from npf_gwwaveform_b200._lib import LIB
+
+    assert LIB.load().npfk_tc_abort_code() == 0, "a tcgen05 kernel gave up on an mbarrier wait"
+
+
+@pytest.mark.parametrize("M,N,K,relu,res_mode", [
+    (128, 128, 128, False, "none"), (300, 128, 128, True, "none"), (4096, 128, 32, True, "full"),
+    (1000, 256, 128, False, "full"), (3 * 512, 128, 128, True, "tiled"), (777, 64, 256, True, "none"),
+    (5000, 512, 256, False, "none"), (2049, 16, 128, False, "none"), (640, 128, 48, True, "none"),
+    (100, 128, 128, True, "none"),      # M < 128: stays on the FFMA kernel
+    (70000, 128, 128, True, "none"),    # more tiles than CTAs: persistent loop + TMEM double buffering
+])
+def test_linear_fast(M, N, K, relu, res_mode):
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    g = torch.Generator().manual_seed(M + N + K)
+    x, w, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / math.sqrt(K), torch.randn(N, generator=g)
+    res = None
+    if res_mode == "full":
+        res = torch.randn(M, N, generator=g)
+    elif res_mode == "tiled":
+        res = torch.randn(M // 3, N, generator=g)
+    dy = torch.randn(M, N, generator=g)
+
+    xs, ws, bs = (t.double().requires_grad_(True) for t in (x, w, b))
+    rs = res.double().requires_grad_(True) if res is not None else None
+    y_ref = xs @ ws.t() + bs
+    if rs is not None:
+        y_ref = y_ref + (rs if res_mode == "full" else rs.repeat(3, 1))
+    if relu:
+        y_ref = torch.relu(y_ref)
+    y_ref.backward(dy.double())
+
+    xd, wd, bd = (t.cuda().requires_grad_(True) for t in (x, w, b))
+    rd = res.cuda().requires_grad_(True) if res is not None else None
+    y = Kn.linear(xd, wd, bd, res=rd, relu=relu)
+    y.backward(dy.cuda())
+    assert rel_err(y, y_ref) < TOL, ("y", rel_err(y, y_ref))
+    for n, a, r in (("dx", xd.grad, xs.grad), ("dw", wd.grad, ws.grad), ("db", bd.grad, bs.grad)):
+        assert rel_err(a, r) < TOL, (n, rel_err(a, r))
+    if rd is not None:
+        assert rel_err(rd.grad, rs.grad) < TOL
+
+
+def test_linear_fast_strided():
+    """operands that are column slices of wider tensors (split r_z_merger, SetConv output with a density column)"""
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    g = torch.Generator().manual_seed(5)
+    W = torch.randn(128, 256, generator=g) / 16
+    X = torch.randn(4, 300, 160, generator=g)
+    Wd, Xd = W.cuda().requires_grad_(True), X.cuda().requires_grad_(True)
+    y = Kn.linear(Xd[..., 32:160], Wd[:, 128:])
+    y.square().sum().backward()
+    Ws, Xs = W.double().requires_grad_(True), X.double().requires_grad_(True)
+    y_ref = Xs[..., 32:160] @ Ws[:, 128:].t()
+    y_ref.square().sum().backward()
+    assert rel_err(y, y_ref) < TOL
+    assert rel_err(Wd.grad, Ws.grad) < TOL
+    assert rel_err(Xd.grad, Xs.grad) < TOL
