@@ -89,13 +89,14 @@ int npfk_set_mean_bwd(const float* dout, float* dx, int B, int64_t N, int C, voi
  * feature dimension (no permute copies), logits are never materialised (online softmax).
  *   q:[B,Nq,H*D] k,v:[B,Nk,H*D] -> out:[B,Nq,H*D], lse:[B,H,Nq] (log-sum-exp of scaled logits)
  * D in {4,8,16,32,64,128}.  H=1, D=kq_size gives DotAttender("scaledot").
+ * mode NPFK_MODE_FAST with D in {16,32} and H*D a multiple of 32 runs the tcgen05/TMEM kernels (tf32 operands).
  */
 int npfk_mha_fwd(const float* q, const float* k, const float* v, float* out, float* lse, int B, int64_t Nq,
-                 int64_t Nk, int H, int D, float scale, void* stream);
+                 int64_t Nk, int H, int D, float scale, int mode, void* stream);
 /* dq,dk,dv have the layouts of q,k,v (overwritten).  delta_ws:[B*H*Nq] caller workspace (sum_d dO*O). */
 int npfk_mha_bwd(const float* q, const float* k, const float* v, const float* out, const float* lse,
                  const float* dout, float* dq, float* dk, float* dv, float* delta_ws, int B, int64_t Nq, int64_t Nk,
-                 int H, int D, float scale, void* stream);
+                 int H, int D, float scale, int mode, void* stream);
 
 /* ---- residual + LayerNorm ---------------------------------------------------------------------
  * LN(a + b) of TransformerAttender.forward (attention.py:583-588).  b may be NULL.

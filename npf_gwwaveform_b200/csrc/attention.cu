@@ -259,6 +259,13 @@ static int launch_bwd(const float* q, const float* k, const float* v, const floa
     return check_launch("mha_bwd_dkv");
 }
 
+namespace tc {
+bool attn_tc_eligible(const float* q, const float* k, const float* v, const float* out, int B, int64_t Nq, int64_t Nk,
+                      int H, int D);
+int attn_fwd_tc(const float* q, const float* k, const float* v, float* out, float* lse, int B, int64_t Nq, int64_t Nk,
+                int H, int D, float scale, cudaStream_t st);
+}  // namespace tc
+
 }  // namespace npfk
 
 using namespace npfk;
@@ -279,18 +286,21 @@ using namespace npfk;
 extern "C" {
 
 int npfk_mha_fwd(const float* q, const float* k, const float* v, float* out, float* lse, int B, int64_t Nq, int64_t Nk,
-                 int H, int D, float scale, void* stream) {
+                 int H, int D, float scale, int mode, void* stream) {
     NPFK_REQUIRE(q && k && v && out && lse, "mha_fwd: null pointer");
     NPFK_REQUIRE(B > 0 && Nq > 0 && Nk > 0 && H > 0, "mha_fwd: bad shape B=%d Nq=%lld Nk=%lld H=%d", B, (long long)Nq,
                  (long long)Nk, H);
     NPFK_REQUIRE(H <= 65535 && B <= 65535, "mha_fwd: H and B must be <= 65535");
     cudaStream_t st = as_stream(stream);
+    if (mode == NPFK_MODE_FAST && tc::attn_tc_eligible(q, k, v, out, B, Nq, Nk, H, D))
+        return tc::attn_fwd_tc(q, k, v, out, lse, B, Nq, Nk, H, D, scale, st);
     NPFK_ATTN_DISPATCH(launch_fwd, q, k, v, out, lse, B, Nq, Nk, H, scale, st)
 }
 
 int npfk_mha_bwd(const float* q, const float* k, const float* v, const float* out, const float* lse, const float* dout,
                  float* dq, float* dk, float* dv, float* delta_ws, int B, int64_t Nq, int64_t Nk, int H, int D,
-                 float scale, void* stream) {
+                 float scale, int mode, void* stream) {
+    (void)mode;
     NPFK_REQUIRE(q && k && v && out && lse && dout && dq && dk && dv && delta_ws, "mha_bwd: null pointer");
     NPFK_REQUIRE(B > 0 && Nq > 0 && Nk > 0 && H > 0, "mha_bwd: bad shape");
     NPFK_REQUIRE(H <= 65535 && B <= 65535, "mha_bwd: H and B must be <= 65535");

@@ -72,6 +72,13 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* m, uint64_t* bar,
         : "r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* m, uint64_t* bar, void* smem, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        :
+        : "r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                  :
@@ -170,6 +177,15 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
         : "r"(taddr)
         : "memory");
 }
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 __device__ __forceinline__ float round_tf32(float x) {
@@ -183,6 +199,14 @@ __device__ __forceinline__ float round_tf32(float x) {
 // atom32 selects CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B (MN-major tf32 operands).
 int encode_tmap_2d(CUtensorMap* out, const float* base, uint64_t inner, uint64_t outer, uint64_t ld_elems,
                    uint32_t box_rows, bool atom32 = false);
+
+// 3-D fp32 tensor map over a [batch, rows, cols] tensor (cols contiguous, row pitch ld_elems, batch pitch
+// batch_elems): dims {cols, rows, batch}, box {32 floats, box_rows, 1}.  Rows past `rows` read as zero, so a
+// tile never runs into the next batch item.
+int encode_tmap_3d(CUtensorMap* out, const float* base, uint64_t cols, uint64_t rows, uint64_t batch, uint64_t ld_elems,
+                   uint64_t batch_elems, uint32_t box_rows, bool atom32);
+// device address of the global abort flag (see the abort protocol above)
+int* abort_flag_ptr();
 
 }  // namespace tc
 }  // namespace npfk

@@ -72,6 +72,40 @@ int encode_tmap_2d(CUtensorMap* out, const float* base, uint64_t inner, uint64_t
     return NPFK_OK;
 }
 
+int encode_tmap_3d(CUtensorMap* out, const float* base, uint64_t cols, uint64_t rows, uint64_t batch, uint64_t ld_elems,
+                   uint64_t batch_elems, uint32_t box_rows, bool atom32) {
+    static thread_local bool ctx_bound = false;
+    if (!ctx_bound) {
+        (void)cudaFree(nullptr);
+        ctx_bound = true;
+    }
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled is not available from the driver");
+        return NPFK_ERR_CUDA;
+    }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld_elems & 3) || (batch_elems & 3) || cols == 0 || rows == 0 ||
+        batch == 0) {
+        set_error("tensor map: base must be 16-byte aligned and the pitches multiples of 4 floats");
+        return NPFK_ERR_INVALID;
+    }
+    cuuint64_t dims[3] = {cols, rows, batch};
+    cuuint64_t strides[2] = {ld_elems * sizeof(float), batch_elems * sizeof(float)};
+    cuuint32_t box[3] = {32, box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(3d) failed with CUresult %d (cols=%llu rows=%llu batch=%llu ld=%llu)", (int)r,
+                  (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)batch,
+                  (unsigned long long)ld_elems);
+        return NPFK_ERR_CUDA;
+    }
+    return NPFK_OK;
+}
+
 constexpr int kThreads = 192;
 constexpr int kBlockM = 128;        // rows per output tile = UMMA M
 constexpr int kBlockK = 32;         // fp32 elements per 128-byte swizzle row
@@ -443,7 +477,7 @@ tc_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant
 }
 
 // ------------------------------------------------------------------------------------------ host launchers
-static int* abort_flag_ptr() {
+int* abort_flag_ptr() {
     static int* p = nullptr;
     if (!p) {
         void* q = nullptr;

@@ -6,6 +6,7 @@ torch's current stream.  There is no fallback: CPU tensors or a missing libnpfk.
 from __future__ import annotations
 
 import ctypes
+import weakref
 from typing import Optional
 
 import torch
@@ -86,26 +87,31 @@ def _weight_view(w: torch.Tensor):
 _tf32_cache = {}
 
 
+def _tf32_evict(base_id):
+    for k in [k for k in _tf32_cache if k[0] == base_id]:
+        _tf32_cache.pop(k, None)
+
+
 def tf32_weight(w: torch.Tensor) -> torch.Tensor:
     """Round-to-nearest tf32 copy of a weight (tcgen05.mma.kind::tf32 truncates its fp32 operands).
 
-    Cached per (storage, version) outside CUDA-graph capture; inside a capture the rounding kernel is
-    always recorded so that replays see the current weights."""
+    Cached per parameter object (weak reference; views are keyed on their base) and parameter version, outside
+    CUDA-graph capture; inside a capture the rounding kernel is always recorded so replays see current weights."""
+    base = w._base if w._base is not None else w
     wv, _ = _weight_view(w.detach())
     if not wv.is_contiguous():
         wv = wv.contiguous()
     capturing = torch.cuda.is_current_stream_capturing()
-    key = (w.data_ptr(), tuple(w.shape))
+    key = (id(base), w.storage_offset(), tuple(w.shape), tuple(w.stride()))
     if not capturing:
         hit = _tf32_cache.get(key)
-        if hit is not None and hit[0] == w._version:
-            return hit[1]
+        if hit is not None and hit[0]() is base and hit[1] == base._version:
+            return hit[2]
     out = torch.empty_like(wv)
     LIB.call("npfk_round_tf32", _p(wv), _p(out), wv.numel(), _st())
     if not capturing:
-        if len(_tf32_cache) > 4096:
-            _tf32_cache.clear()
-        _tf32_cache[key] = (w._version, out)
+        base_id = id(base)
+        _tf32_cache[key] = (weakref.ref(base, lambda _r, i=base_id: _tf32_evict(i)), base._version, out)
     return out
 
 
@@ -247,20 +253,21 @@ class _MhaFn(Function):
         D = E // n_heads
         out = torch.empty_like(q)
         lse = torch.empty(B, n_heads, Nq, device=q.device, dtype=torch.float32)
-        LIB.call("npfk_mha_fwd", _p(q), _p(k), _p(v), _p(out), _p(lse), B, Nq, Nk, n_heads, D, float(scale), _st())
+        mode = _state["mode"]
+        LIB.call("npfk_mha_fwd", _p(q), _p(k), _p(v), _p(out), _p(lse), B, Nq, Nk, n_heads, D, float(scale), mode, _st())
         ctx.save_for_backward(q, k, v, out, lse)
-        ctx.cfg = (B, Nq, Nk, n_heads, D, float(scale))
+        ctx.cfg = (B, Nq, Nk, n_heads, D, float(scale), mode)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         q, k, v, out, lse = ctx.saved_tensors
-        B, Nq, Nk, H, D, scale = ctx.cfg
+        B, Nq, Nk, H, D, scale, mode = ctx.cfg
         dout = _c(dout)
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
         ws = torch.empty(B * H * Nq, device=q.device, dtype=torch.float32)
         LIB.call("npfk_mha_bwd", _p(q), _p(k), _p(v), _p(out), _p(lse), _p(dout), _p(dq), _p(dk), _p(dv), _p(ws), B, Nq,
-                 Nk, H, D, scale, _st())
+                 Nk, H, D, scale, mode, _st())
         return dq, dk, dv, None, None
 
 

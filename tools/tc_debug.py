@@ -41,3 +41,30 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def via_autograd():
+    import math
+
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    Kn.set_mode("fast")
+    for (M, N, K, relu) in [(300, 128, 128, True), (300, 128, 128, False), (4096, 128, 128, True)]:
+        g = torch.Generator().manual_seed(M + N + K)
+        x, w, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / math.sqrt(K), torch.randn(N, generator=g)
+        dy = torch.randn(M, N, generator=g)
+        xd, wd, bd = (t.cuda().requires_grad_(True) for t in (x, w, b))
+        y = Kn.linear(xd, wd, bd, relu=relu)
+        y.backward(dy.cuda())
+        yr = xd.detach().double() @ wd.detach().double().t() + bd.detach().double()
+        gg = dy.cuda().double() * ((yr > 0) if relu else 1.0)
+        dxr = gg @ wd.detach().double()
+        d = (xd.grad.double() - dxr).abs()
+        i = int(d.argmax())
+        print(M, N, K, relu, "abort", abort(), "dx err", float(d.max() / dxr.abs().max()), "at", divmod(i, K),
+              "bad rows", (d.max(1).values > 1e-2).nonzero().flatten().tolist()[:20],
+              "mask mismatches", int(((y > 0) != (yr > 0)).sum()))
+
+
+if __name__ == "__main__":
+    via_autograd()
