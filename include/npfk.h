@@ -93,7 +93,9 @@ int npfk_set_mean_bwd(const float* dout, float* dx, int B, int64_t N, int C, voi
  */
 int npfk_mha_fwd(const float* q, const float* k, const float* v, float* out, float* lse, int B, int64_t Nq,
                  int64_t Nk, int H, int D, float scale, int mode, void* stream);
-/* dq,dk,dv have the layouts of q,k,v (overwritten).  delta_ws:[B*H*Nq] caller workspace (sum_d dO*O). */
+/* dq,dk,dv have the layouts of q,k,v (overwritten).  delta_ws: caller workspace of npfk_mha_bwd_ws_floats(B,Nq,H)
+ * floats, 16-byte aligned (sum_d dO*O and log2-domain lse, padded to whole query tiles). */
+int64_t npfk_mha_bwd_ws_floats(int B, int64_t Nq, int H);
 int npfk_mha_bwd(const float* q, const float* k, const float* v, const float* out, const float* lse,
                  const float* dout, float* dq, float* dk, float* dv, float* delta_ws, int B, int64_t Nq, int64_t Nk,
                  int H, int D, float scale, int mode, void* stream);

@@ -1,0 +1,473 @@
+// tcgen05 / TMEM / TMA backward of the multi-head cross attention (NPFK_MODE_FAST).
+//
+// Autograd of softmax(Q K^T * scale) V of the reference (npf/architectures/attention.py:129-164, 204-220 with the head
+// split/merge of :507-527), flash style: logits are recomputed from q/k and the saved log-sum-exp, never stored.
+//
+// One CTA owns (batch item, 32-float column box = 32/D heads, tile of 128 keys) and streams the queries in half
+// tiles of 64.  The transposed problem is used so that KEYS sit on the TMEM lanes:
+//     S^T  = K Q^T          (A = K tile, B = Q half tile, both K-major)           128 x 64 in TMEM
+//     dP^T = V dO^T         (A = V tile, B = dO half tile)                        128 x 64 in TMEM
+//   thread = key row:  P^T = exp2(S^T*scale*log2e - lse2[q]),  dS^T = P^T * (dP^T - delta[q])
+//     P^T and dS^T are written back IN PLACE into TMEM (tcgen05.st) and become the A operands of
+//     dV += P^T dO          (A from TMEM, B = dO half tile MN-major)              accumulated over all queries
+//     dK += dS^T Q          (A from TMEM, B = Q half tile MN-major)               accumulated over all queries
+//     dS^T also goes to shared memory (MN-major, 32-byte-atom swizzle) as the A operand of
+//     dQ  = dS K            (M = queries, B = K tile MN-major), reduced into HBM with red.global.add.v4.f32
+//                           because the other key tiles of the same task add to the same rows.
+// scale is folded into the dQ / dK drains.  K, Q and dO are each needed K-major and MN-major; tf32 MN-major
+// operands only exist in the 32-byte-atom swizzle, so TMA loads them twice with two tensor maps (L2 hits).
+//   warp 0      TMA producer         warp 1   TMEM allocator + MMA issuer        warps 2..5  softmax / drains
+#include <math.h>
+
+#include "tc_common.cuh"
+
+namespace npfk {
+namespace tc {
+
+constexpr int kBK = 128;                       // keys per CTA (TMEM lanes)
+constexpr int kBQ = 64;                        // queries per half tile (UMMA N of S^T)
+constexpr int kBStages = 3;
+constexpr int kBThreads = 192;
+constexpr int kBStgBytes = kBK * kBQ * 4;      // 32 KB: dS^T staging, 2 blocks of [128 keys x 32 queries]
+constexpr int kBStgBlock = kBK * 128;          // 16 KB
+constexpr int kBTileQ = kBQ * 128;             // 8 KB: one half tile of a 32-float box
+constexpr int kBStageBytes = 4 * kBTileQ + 1024;   // Q(K-major) Q(MN) dO(K-major) dO(MN) + lse2/delta
+constexpr int kBTileK = kBK * 128;             // 16 KB
+constexpr int kBStgOff = 0;
+constexpr int kBStageOff = 2 * kBStgBytes;                       // 65536
+constexpr int kBKkmOff = kBStageOff + kBStages * kBStageBytes;   // 166912
+constexpr int kBKmnOff = kBKkmOff + kBTileK;
+constexpr int kBVOff = kBKmnOff + kBTileK;
+constexpr int kBBarOff = kBVOff + kBTileK;                       // 216064
+constexpr int kBNumBars = 1 + 2 * kBStages + 9;
+constexpr int kBSmem = 1024 + kBBarOff + kBNumBars * 8 + 16;
+constexpr uint32_t kBTmemCols = 512;
+constexpr uint32_t kBTmemAcc = 256;            // dK / dV accumulators
+constexpr uint32_t kBTmemDq = 384;             // two dQ accumulators of 32 columns
+
+struct AttnBwdParams {
+    float* dq;            // [B, Nq, E]  "+=" (zero-filled by the host wrapper)
+    float* dk;            // [B, Nk, E]
+    float* dv;
+    const float* ws;      // lse2_pad [B,H,Nqp] then delta_pad [B,H,Nqp]
+    int B, H, E;
+    int64_t Nq, Nk, Nqp;
+    float scale;
+    int k_tiles, half_tiles, nsplit, tiles_per_split;
+    int nh;               // UMMA N of the dV / dK / dQ products (16: one head, 32: whole box)
+    int* g_abort;
+};
+
+// delta[b,h,q] = sum_d dO*O, lse2 = lse * log2(e); both padded to a multiple of 64 queries (+inf / 0) so that the
+// main kernel can fetch them with aligned 1-D bulk copies and padded queries get P = 0.
+__global__ void attn_bwd_prep_kernel(const float* __restrict__ out, const float* __restrict__ dout,
+                                     const float* __restrict__ lse, float* __restrict__ ws, int B, int H, int D,
+                                     int64_t Nq, int64_t Nqp) {
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int bh = blockIdx.y;
+    if (q >= Nqp) return;
+    const int b = bh / H, h = bh % H;
+    float delta = 0.f, l2 = INFINITY;
+    if (q < Nq) {
+        const int64_t off = ((int64_t)b * Nq + q) * (H * D) + h * D;
+        const float4* o4 = reinterpret_cast<const float4*>(out + off);
+        const float4* d4 = reinterpret_cast<const float4*>(dout + off);
+        for (int i = 0; i < D / 4; ++i) {
+            const float4 a = __ldg(o4 + i), g = __ldg(d4 + i);
+            delta = fmaf(a.x, g.x, delta);
+            delta = fmaf(a.y, g.y, delta);
+            delta = fmaf(a.z, g.z, delta);
+            delta = fmaf(a.w, g.w, delta);
+        }
+        l2 = __ldg(lse + (int64_t)bh * Nq + q) * 1.4426950408889634f;
+    }
+    ws[(int64_t)bh * Nqp + q] = l2;
+    ws[((int64_t)B * H + bh) * Nqp + q] = delta;
+}
+
+struct BwdBars {
+    uint64_t* kv_full;
+    uint64_t* st_full;
+    uint64_t* st_empty;
+    uint64_t* s_full;
+    uint64_t* p_ready;
+    uint64_t* dq_full;
+    uint64_t* dq_empty;
+    uint64_t* fin;
+};
+
+__device__ __forceinline__ float ex2_approx_b(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <int D>
+__global__ void __launch_bounds__(kBThreads, 1)
+attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_constant__ CUtensorMap tmQm,
+                   const __grid_constant__ CUtensorMap tmOk, const __grid_constant__ CUtensorMap tmOm,
+                   const __grid_constant__ CUtensorMap tmKk, const __grid_constant__ CUtensorMap tmKm,
+                   const __grid_constant__ CUtensorMap tmVk, const AttnBwdParams p) {
+    constexpr int HB = 32 / D;     // heads per 32-float box
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + kBBarOff);
+    BwdBars bar;
+    bar.kv_full = bars;
+    bar.st_full = bars + 1;
+    bar.st_empty = bar.st_full + kBStages;
+    bar.s_full = bar.st_empty + kBStages;
+    bar.p_ready = bar.s_full + 2;
+    bar.dq_full = bar.s_full + 4;
+    bar.dq_empty = bar.s_full + 6;
+    bar.fin = bar.s_full + 8;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + kBNumBars);
+    volatile int* cta_abort = reinterpret_cast<volatile int*>(tmem_ptr + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int boxes = p.E / 32;
+    int idx = blockIdx.x;
+    const int split = idx % p.nsplit;  idx /= p.nsplit;
+    const int kt = idx % p.k_tiles;    idx /= p.k_tiles;
+    const int box = idx % boxes;
+    const int b = idx / boxes;
+    const int ht_begin = split * p.tiles_per_split;
+    const int ht_end = min(p.half_tiles, ht_begin + p.tiles_per_split);
+    const int U = (ht_end - ht_begin) * HB;                 // units = (half tile, head)
+    const int NH = p.nh;
+    const uint32_t head_mn_off = (NH == 16) ? 64u : 0u;     // byte offset of head 1 inside an MN-major row
+    const uint32_t head_col = (NH == 16) ? 0u : (uint32_t)D; // column offset of head 1 inside a 32-wide accumulator
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmQk); prefetch_tmap(&tmQm); prefetch_tmap(&tmOk); prefetch_tmap(&tmOm);
+        prefetch_tmap(&tmKk); prefetch_tmap(&tmKm); prefetch_tmap(&tmVk);
+        mbar_init(bar.kv_full, 1);
+        for (int i = 0; i < kBStages; ++i) {
+            mbar_init(&bar.st_full[i], 1);
+            mbar_init(&bar.st_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&bar.s_full[i], 1);
+            mbar_init(&bar.p_ready[i], 4);
+            mbar_init(&bar.dq_full[i], 1);
+            mbar_init(&bar.dq_empty[i], 2);
+        }
+        mbar_init(bar.fin, 1);
+        *cta_abort = 0;
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr, kBTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0 && U > 0) {   // ---------------------------------------------------------- TMA producer
+            mbar_arrive_expect_tx(bar.kv_full, 3u * kBTileK);
+            tma_load_3d(&tmKk, bar.kv_full, base + kBKkmOff, box * 32, kt * kBK, b);
+            tma_load_3d(&tmKm, bar.kv_full, base + kBKmnOff, box * 32, kt * kBK, b);
+            tma_load_3d(&tmVk, bar.kv_full, base + kBVOff, box * 32, kt * kBK, b);
+            const int64_t bh0 = (int64_t)b * p.H + box * HB;
+            for (int ht = ht_begin; ht < ht_end; ++ht) {
+                const uint32_t i = (uint32_t)(ht - ht_begin);
+                const uint32_t st = i % kBStages, ph = (i / kBStages) & 1;
+                if (!mbar_wait(&bar.st_empty[st], ph ^ 1, cta_abort, p.g_abort, 41)) break;
+                uint8_t* s = base + kBStageOff + st * kBStageBytes;
+                mbar_arrive_expect_tx(&bar.st_full[st], 4u * kBTileQ + (uint32_t)HB * 512u);
+                tma_load_3d(&tmQk, &bar.st_full[st], s, box * 32, ht * kBQ, b);
+                tma_load_3d(&tmQm, &bar.st_full[st], s + kBTileQ, box * 32, ht * kBQ, b);
+                tma_load_3d(&tmOk, &bar.st_full[st], s + 2 * kBTileQ, box * 32, ht * kBQ, b);
+                tma_load_3d(&tmOm, &bar.st_full[st], s + 3 * kBTileQ, box * 32, ht * kBQ, b);
+                for (int hb = 0; hb < HB; ++hb) {
+                    const float* l2 = p.ws + (bh0 + hb) * p.Nqp + (int64_t)ht * kBQ;
+                    bulk_load_1d(s + 4 * kBTileQ + hb * 512, l2, 256, &bar.st_full[st]);
+                    bulk_load_1d(s + 4 * kBTileQ + hb * 512 + 256, l2 + (int64_t)p.B * p.H * p.Nqp, 256, &bar.st_full[st]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && U > 0) {   // ---------------------------------------------------------- MMA issuer
+            const uint32_t idesc_s = make_idesc_tf32(kBQ, false, false);
+            const uint32_t idesc_kv = make_idesc_tf32(NH, false, true);    // A from TMEM, B MN-major
+            const uint32_t idesc_dq = make_idesc_tf32(NH, true, true);     // A, B MN-major
+            const uint32_t kkm = smem_u32(base + kBKkmOff), kmn = smem_u32(base + kBKmnOff), vkm = smem_u32(base + kBVOff);
+            const uint32_t stg0 = smem_u32(base + kBStgOff), stage0 = smem_u32(base + kBStageOff);
+            auto issue_s = [&](int u) -> bool {     // S^T and dP^T of unit u
+                const int i = u / HB, hb = u % HB;
+                const uint32_t st = (uint32_t)i % kBStages;
+                if (hb == 0) {
+                    if (!mbar_wait(&bar.st_full[st], ((uint32_t)i / kBStages) & 1, cta_abort, p.g_abort, 42)) return false;
+                    tc_fence_after();
+                }
+                const uint32_t sa = stage0 + st * kBStageBytes;
+                const uint32_t koff = (uint32_t)(hb * D * 4);
+                const uint32_t tS = tmem_base + (uint32_t)(u & 1) * 128u;
+#pragma unroll
+                for (int s = 0; s < D / 8; ++s)
+                    umma_tf32(tS, make_sdesc_sw128(kkm + koff + s * 32, 16, 1024),
+                              make_sdesc_sw128(sa + koff + s * 32, 16, 1024), idesc_s, s > 0);
+#pragma unroll
+                for (int s = 0; s < D / 8; ++s)
+                    umma_tf32(tS + 64, make_sdesc_sw128(vkm + koff + s * 32, 16, 1024),
+                              make_sdesc_sw128(sa + 2 * kBTileQ + koff + s * 32, 16, 1024), idesc_s, s > 0);
+                umma_commit(&bar.s_full[u & 1]);
+                return true;
+            };
+            auto role = [&]() {
+                if (!mbar_wait(bar.kv_full, 0, cta_abort, p.g_abort, 43)) return;
+                tc_fence_after();
+                if (!issue_s(0)) return;
+                for (int u = 0; u < U; ++u) {
+                    if (u + 1 < U && !issue_s(u + 1)) return;
+                    const int i = u / HB, hb = u % HB;
+                    const uint32_t st = (uint32_t)i % kBStages, set = (uint32_t)u & 1, ph = ((uint32_t)u >> 1) & 1;
+                    if (!mbar_wait(&bar.p_ready[set], ph, cta_abort, p.g_abort, 44)) return;
+                    if (!mbar_wait(&bar.dq_empty[set], ph ^ 1, cta_abort, p.g_abort, 45)) return;
+                    tc_fence_after();
+                    const uint32_t sa = stage0 + st * kBStageBytes;
+                    const uint32_t tS = tmem_base + set * 128u;
+                    const uint32_t hoff = (uint32_t)hb * head_mn_off;
+                    const uint32_t acc = tmem_base + kBTmemAcc + (uint32_t)hb * 2u * (uint32_t)NH;
+                    const uint32_t first = (i == 0) ? 0u : 1u;
+#pragma unroll
+                    for (int j = 0; j < kBQ / 8; ++j)      // dV += P^T dO
+                        umma_tf32_ts(acc + NH, tS + 8 * j, make_sdesc_mn32(sa + 3 * kBTileQ + j * 1024 + hoff, 16384, 512),
+                                     idesc_kv, first | (uint32_t)(j > 0));
+#pragma unroll
+                    for (int j = 0; j < kBQ / 8; ++j)      // dK += dS^T Q
+                        umma_tf32_ts(acc, tS + 64 + 8 * j, make_sdesc_mn32(sa + kBTileQ + j * 1024 + hoff, 16384, 512),
+                                     idesc_kv, first | (uint32_t)(j > 0));
+#pragma unroll
+                    for (int j = 0; j < kBK / 8; ++j)      // dQ = dS K   (rows 64..127 of the accumulator are unused)
+                        umma_tf32(tmem_base + kBTmemDq + set * 32u, make_sdesc_mn32(stg0 + set * kBStgBytes + j * 1024, kBStgBlock, 512),
+                                  make_sdesc_mn32(kmn + j * 1024 + hoff, 16384, 512), idesc_dq, j > 0);
+                    umma_commit(&bar.dq_full[set]);
+                    if (hb == HB - 1) umma_commit(&bar.st_empty[st]);
+                }
+                umma_commit(bar.fin);
+            };
+            role();
+        }
+    } else {
+        // ------------------------------------------------------------------------------ softmax / drain warps
+        const int qd = warp & 3;                       // TMEM lane quarter this warp may access
+        const int kk = qd * 32 + lane;                 // key row inside the tile
+        const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+        const float k2 = p.scale * 1.4426950408889634f;
+        const bool key_ok = (int64_t)kt * kBK + kk < p.Nk;
+        const uint32_t sw = (uint32_t)(kk & 3);
+        const uint32_t hsel = (uint32_t)((kk >> 2) & 1);   // alternate the 16-byte halves: conflict-free staging stores
+        auto wait_all = [&](uint64_t* bb, uint32_t ph, int code) -> bool {
+            bool ok = mbar_wait(bb, ph, cta_abort, p.g_abort, code);
+            return __all_sync(0xffffffffu, ok);
+        };
+        // dQ of unit u: rows 0..63 of the accumulator = the 64 queries of the half tile (lane quarters 0 and 1)
+        auto drain_dq = [&](int u) -> bool {
+            const uint32_t set = (uint32_t)u & 1;
+            if (!wait_all(&bar.dq_full[set], ((uint32_t)u >> 1) & 1, 51)) return false;
+            if (qd < 2) {
+                tc_fence_after();
+                const int i = u / HB, hb = u % HB;
+                uint32_t r[D];
+                const uint32_t ta = lane_base + kBTmemDq + set * 32u + (uint32_t)hb * head_col;
+                if constexpr (D == 16) tmem_ld_32x16(ta, r);
+                else tmem_ld_32x32(ta, r);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar.dq_empty[set]);
+                const int64_t q = (int64_t)(ht_begin + i) * kBQ + kk;
+                if (q < p.Nq) {
+                    float* dst = p.dq + ((int64_t)b * p.Nq + q) * p.E + box * 32 + hb * D;
+#pragma unroll
+                    for (int d4 = 0; d4 < D / 4; ++d4)
+                        red_add_v4(dst + 4 * d4, __uint_as_float(r[4 * d4]) * p.scale, __uint_as_float(r[4 * d4 + 1]) * p.scale,
+                                   __uint_as_float(r[4 * d4 + 2]) * p.scale, __uint_as_float(r[4 * d4 + 3]) * p.scale);
+                }
+            }
+            return true;
+        };
+        auto role = [&]() {
+            for (int u = 0; u < U; ++u) {
+                const int i = u / HB, hb = u % HB;
+                const uint32_t set = (uint32_t)u & 1, st = (uint32_t)i % kBStages;
+                if (u >= 2 && !drain_dq(u - 2)) return;          // also frees staging[set]
+                if (hb == 0 && !wait_all(&bar.st_full[st], ((uint32_t)i / kBStages) & 1, 52)) return;
+                if (!wait_all(&bar.s_full[set], ((uint32_t)u >> 1) & 1, 53)) return;
+                tc_fence_after();
+                const uint8_t* stats = base + kBStageOff + st * kBStageBytes + 4 * kBTileQ + hb * 512;
+                uint8_t* stg = base + kBStgOff + set * kBStgBytes + kk * 128;
+                const uint32_t tS = lane_base + set * 128u;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {                    // 32 queries at a time
+                    uint32_t s[32], g[32];
+                    tmem_ld_32x32(tS + c * 32, s);
+                    tmem_ld_32x32(tS + 64 + c * 32, g);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 l2 = *reinterpret_cast<const float4*>(stats + (c * 32 + j4 * 4) * 4);
+                        const float4 dl = *reinterpret_cast<const float4*>(stats + 256 + (c * 32 + j4 * 4) * 4);
+                        const float l2a[4] = {l2.x, l2.y, l2.z, l2.w}, dla[4] = {dl.x, dl.y, dl.z, dl.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int j = j4 * 4 + e;
+                            float pv = ex2_approx_b(fmaf(__uint_as_float(s[j]), k2, -l2a[e]));
+                            pv = key_ok ? pv : 0.f;
+                            const float ds = pv * (__uint_as_float(g[j]) - dla[e]);
+                            s[j] = __float_as_uint(pv);
+                            g[j] = __float_as_uint(ds);
+                        }
+                    }
+                    tmem_st_32x32(tS + c * 32, s);
+                    tmem_st_32x32(tS + 64 + c * 32, g);
+                    // dS^T row of this key into the MN-major staging block c: 32-byte chunk ch at (ch ^ (kk & 3))
+                    uint8_t* blk = stg + c * kBStgBlock;
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) {
+                        const uint32_t ch = (uint32_t)t >> 1, half = ((uint32_t)t & 1) ^ hsel;
+                        const int j = (int)(ch * 8 + half * 4);
+                        *reinterpret_cast<float4*>(blk + ((ch ^ sw) << 5) + (half << 4)) =
+                            make_float4(__uint_as_float(g[j]), __uint_as_float(g[j + 1]), __uint_as_float(g[j + 2]),
+                                        __uint_as_float(g[j + 3]));
+                    }
+                }
+                tmem_st_wait();
+                fence_proxy_async();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar.p_ready[set]);
+            }
+            for (int u = max(0, U - 2); u < U; ++u)
+                if (!drain_dq(u)) return;
+            // ---- dK / dV of this key tile
+            if (!wait_all(bar.fin, 0, 54)) return;
+            tc_fence_after();
+            const int64_t key = (int64_t)kt * kBK + kk;
+#pragma unroll
+            for (int hb = 0; hb < HB; ++hb) {
+                uint32_t rk[D], rv[D];
+                const uint32_t acc = lane_base + kBTmemAcc + (uint32_t)hb * 2u * (uint32_t)NH + (uint32_t)hb * head_col;
+                if constexpr (D == 16) {
+                    tmem_ld_32x16(acc, rk);
+                    tmem_ld_32x16(acc + NH, rv);
+                } else {
+                    tmem_ld_32x32(acc, rk);
+                    tmem_ld_32x32(acc + NH, rv);
+                }
+                tmem_ld_wait();
+                if (key < p.Nk) {
+                    const int64_t off = ((int64_t)b * p.Nk + key) * p.E + box * 32 + hb * D;
+#pragma unroll
+                    for (int d4 = 0; d4 < D / 4; ++d4) {
+                        const float4 a = make_float4(__uint_as_float(rk[4 * d4]) * p.scale, __uint_as_float(rk[4 * d4 + 1]) * p.scale,
+                                                     __uint_as_float(rk[4 * d4 + 2]) * p.scale, __uint_as_float(rk[4 * d4 + 3]) * p.scale);
+                        const float4 c = make_float4(__uint_as_float(rv[4 * d4]), __uint_as_float(rv[4 * d4 + 1]),
+                                                     __uint_as_float(rv[4 * d4 + 2]), __uint_as_float(rv[4 * d4 + 3]));
+                        if (p.nsplit == 1) {
+                            *reinterpret_cast<float4*>(p.dk + off + 4 * d4) = a;
+                            *reinterpret_cast<float4*>(p.dv + off + 4 * d4) = c;
+                        } else {
+                            red_add_v4(p.dk + off + 4 * d4, a.x, a.y, a.z, a.w);
+                            red_add_v4(p.dv + off + 4 * d4, c.x, c.y, c.z, c.w);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+        };
+        if (U > 0) role();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kBTmemCols);
+    }
+}
+
+int64_t attn_bwd_ws_floats(int B, int64_t Nq, int H) {
+    const int64_t nqp = (Nq + kBQ - 1) / kBQ * kBQ;
+    return 2 * (int64_t)B * H * nqp;
+}
+
+int attn_bwd_tc(const float* q, const float* k, const float* v, const float* out, const float* lse, const float* dout,
+                float* dq, float* dk, float* dv, float* ws, int B, int64_t Nq, int64_t Nk, int H, int D, float scale,
+                cudaStream_t st) {
+    const int E = H * D;
+    if ((reinterpret_cast<uintptr_t>(ws) & 15) || (reinterpret_cast<uintptr_t>(dq) & 15) ||
+        (reinterpret_cast<uintptr_t>(dk) & 15) || (reinterpret_cast<uintptr_t>(dv) & 15) ||
+        (reinterpret_cast<uintptr_t>(dout) & 15)) {
+        set_error("attn_bwd_tc: pointers must be 16-byte aligned");
+        return NPFK_ERR_INVALID;
+    }
+    CUtensorMap tmQk, tmQm, tmOk, tmOm, tmKk, tmKm, tmVk;
+    int rc = encode_tmap_3d(&tmQk, q, E, Nq, B, E, (uint64_t)Nq * E, kBQ, false);
+    if (!rc) rc = encode_tmap_3d(&tmQm, q, E, Nq, B, E, (uint64_t)Nq * E, kBQ, true);
+    if (!rc) rc = encode_tmap_3d(&tmOk, dout, E, Nq, B, E, (uint64_t)Nq * E, kBQ, false);
+    if (!rc) rc = encode_tmap_3d(&tmOm, dout, E, Nq, B, E, (uint64_t)Nq * E, kBQ, true);
+    if (!rc) rc = encode_tmap_3d(&tmKk, k, E, Nk, B, E, (uint64_t)Nk * E, kBK, false);
+    if (!rc) rc = encode_tmap_3d(&tmKm, k, E, Nk, B, E, (uint64_t)Nk * E, kBK, true);
+    if (!rc) rc = encode_tmap_3d(&tmVk, v, E, Nk, B, E, (uint64_t)Nk * E, kBK, false);
+    if (rc) return rc;
+
+    AttnBwdParams p{};
+    p.dq = dq; p.dk = dk; p.dv = dv; p.ws = ws;
+    p.B = B; p.H = H; p.E = E;
+    p.Nq = Nq; p.Nk = Nk;
+    p.Nqp = (Nq + kBQ - 1) / kBQ * kBQ;
+    p.scale = scale;
+    p.k_tiles = (int)((Nk + kBK - 1) / kBK);
+    p.half_tiles = (int)(p.Nqp / kBQ);
+    const int64_t items = (int64_t)B * (E / 32) * p.k_tiles;
+    int64_t ns = (2 * kNumSMs + items - 1) / items;
+    if (ns < 1) ns = 1;
+    if (ns > p.half_tiles) ns = p.half_tiles;
+    p.tiles_per_split = (int)((p.half_tiles + ns - 1) / ns);
+    p.nsplit = (p.half_tiles + p.tiles_per_split - 1) / p.tiles_per_split;
+    static int nh_env = -1;
+    if (nh_env < 0) {
+        const char* e = getenv("NPFK_ATTN_BWD_NH");
+        nh_env = e ? atoi(e) : 0;
+    }
+    p.nh = (D == 16) ? ((nh_env == 32) ? 32 : 16) : 32;
+    p.g_abort = abort_flag_ptr();
+
+    // prep: delta and lse*log2e into the padded workspace; dq (and dk/dv when the queries are split) are "+="
+    {
+        dim3 grid((unsigned)((p.Nqp + 255) / 256), (unsigned)(B * H));
+        attn_bwd_prep_kernel<<<grid, 256, 0, st>>>(out, dout, lse, ws, B, H, D, Nq, p.Nqp);
+        count_launch();
+    }
+    cudaMemsetAsync(dq, 0, sizeof(float) * (size_t)B * Nq * E, st);
+    if (p.nsplit > 1) {
+        cudaMemsetAsync(dk, 0, sizeof(float) * (size_t)B * Nk * E, st);
+        cudaMemsetAsync(dv, 0, sizeof(float) * (size_t)B * Nk * E, st);
+    }
+    static bool attr_done[2] = {false, false};
+    const int di = D == 16 ? 0 : 1;
+    if (!attr_done[di]) {
+        cudaError_t e = D == 16 ? cudaFuncSetAttribute(attn_bwd_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBSmem)
+                                : cudaFuncSetAttribute(attn_bwd_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBSmem);
+        if (e != cudaSuccess) {
+            set_error("attn_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+            return NPFK_ERR_CUDA;
+        }
+        attr_done[di] = true;
+    }
+    const int64_t grid = items * p.nsplit;
+    if (grid > 2147483647LL) {
+        set_error("attn_bwd_tc: grid too large");
+        return NPFK_ERR_INVALID;
+    }
+    if (D == 16)
+        attn_bwd_tc_kernel<16><<<(unsigned)grid, kBThreads, kBSmem, st>>>(tmQk, tmQm, tmOk, tmOm, tmKk, tmKm, tmVk, p);
+    else
+        attn_bwd_tc_kernel<32><<<(unsigned)grid, kBThreads, kBSmem, st>>>(tmQk, tmQm, tmOk, tmOm, tmKk, tmKm, tmVk, p);
+    count_launch();
+    return check_launch("attn_bwd_tc");
+}
+
+}  // namespace tc
+}  // namespace npfk

@@ -265,7 +265,7 @@ class _MhaFn(Function):
         B, Nq, Nk, H, D, scale, mode = ctx.cfg
         dout = _c(dout)
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
-        ws = torch.empty(B * H * Nq, device=q.device, dtype=torch.float32)
+        ws = torch.empty(int(LIB.load().npfk_mha_bwd_ws_floats(B, Nq, H)), device=q.device, dtype=torch.float32)
         LIB.call("npfk_mha_bwd", _p(q), _p(k), _p(v), _p(out), _p(lse), _p(dout), _p(dq), _p(dk), _p(dv), _p(ws), B, Nq,
                  Nk, H, D, scale, mode, _st())
         return dq, dk, dv, None, None
