@@ -62,8 +62,19 @@ class MLP(nn.Module):
             return K.linear(x, layer.weight, layer.bias, relu=True)
         return self.activation(K.linear(x, layer.weight, layer.bias))   # user activation: module composition
 
-    def forward(self, x, res=None, out_relu=False):
-        """``res`` / ``out_relu`` fuse ``relu(res + MLP(x))`` (the sum-merge) into the last layer's epilogue."""
+    def is_plain_relu_chain(self):
+        """True when the whole MLP can run as one K.mlp_chain node (ReLU, no dropout, no residual links)."""
+        return isinstance(self.activation, nn.ReLU) and isinstance(self.dropout, nn.Identity) and not self.is_res
+
+    def forward(self, x, res=None, out_relu=False, x_is_relu=False, dy_premasked=False):
+        """``res`` / ``out_relu`` fuse ``relu(res + MLP(x))`` (the sum-merge) into the last layer's epilogue.
+        ``x_is_relu`` / ``dy_premasked``: see kernels._MlpChainFn (ReLU backward fused across the sum-merge)."""
+        if self.is_plain_relu_chain():
+            layers = [(self.to_hidden.weight, self.to_hidden.bias)]
+            layers += [(lin.weight, lin.bias) for lin in self.linears]
+            layers.append((self.out.weight, self.out.bias))
+            return K.mlp_chain(x, layers, res=res, out_relu=out_relu, x_is_relu=x_is_relu, dy_premasked=dy_premasked)
+        assert not (x_is_relu or dy_premasked)
         h = self.dropout(self._hidden(self.to_hidden, x))
         for lin in self.linears:
             o = self._hidden(lin, h)
@@ -124,12 +135,23 @@ class MergeFlatInputs(nn.Module):
             return K.bcast_add_relu(x1, r)
         # Case B: same rows (x2 possibly with a leading n_z dim that x1 is tiled over): fuse into the epilogue
         if x2.shape[-x1.dim():-1] == x1.shape[:-1] and x2.dim() in (x1.dim(), x1.dim() + 1):
+            if self._fused_relu_bwd():
+                # merged feeds only flat_module, whose first dgrad masks with merged > 0: the resizer skips its own
+                merged = self.resizer(x2, res=x1, out_relu=True, dy_premasked=True)
+                return self.flat_module(merged, x_is_relu=True), True
             return self.resizer(x2, res=x1, out_relu=True)
         return torch.relu(x1 + self.resizer(x2))                     # exotic broadcasting: plain composition
+
+    def _fused_relu_bwd(self):
+        fm = self.flat_module
+        return (type(fm) is MLP and fm.is_plain_relu_chain() and self.resizer.is_plain_relu_chain()
+                and torch.is_grad_enabled())
 
     def forward(self, x1, x2):
         if self.is_sum_merge:
             merged = self._sum_merge(x1, x2)
+            if isinstance(merged, tuple):
+                return merged[0]
         else:
             if x2.dim() == x1.dim() + 1:
                 x1 = x1.unsqueeze(0).expand(x2.shape[0], *x1.shape)

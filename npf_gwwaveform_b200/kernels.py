@@ -188,6 +188,114 @@ def linear(x, w, b=None, res=None, relu=False):
     return _LinearFn.apply(x, w, b, res, relu)
 
 
+class _MlpChainFn(Function):
+    """A whole ReLU MLP (npf/architectures/mlp.py:95-109) as ONE autograd node.
+
+    forward:  h_0 = x ; h_i = relu(h_{i-1} W_i^T + b_i) ; y = act(h_{L-1} W_L^T + b_L + res)
+    backward: the ReLU mask of layer i-1 is applied in the dgrad epilogue of layer i, so no separate
+    elementwise ReLU-backward passes exist inside the chain.  Two flags extend this across the sum-merge
+    (encoders.py:175-183) where the output of one chain (after ReLU) is the input of the next:
+      x_is_relu   the input x is itself a ReLU output -> dx is masked with x > 0 in the first layer's dgrad;
+      dy_premasked  the consumer of y already masked the incoming gradient with y > 0 (it has x_is_relu set),
+                  so the out_relu backward is the identity here.
+    args = (x, res, w_1, b_1, ..., w_L, b_L); b_i may be None.
+    """
+
+    @staticmethod
+    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, x, res, *wb):
+        require_cuda(x, res, *wb)
+        n_layers = len(wb) // 2
+        mode = _state["mode"]
+        lead = x.shape[:-1]
+        M = 1
+        for s in lead:
+            M *= s
+        st = _st()
+        h, ldh = _rows_view(x)
+        acts = [h]
+        wvs, dims = [], []
+        for i in range(n_layers):
+            w, b = wb[2 * i], wb[2 * i + 1]
+            N, Kd = w.shape
+            if mode == MODE_FAST:
+                wv = tf32_weight(w)
+                ldw = wv.shape[1]
+            else:
+                wv, ldw = _weight_view(w)
+            last = i == n_layers - 1
+            bv = _c(b)
+            resv, res_rows = None, 0
+            if last and res is not None:
+                resv = _c(res)
+                res_rows = resv.numel() // N
+                if res_rows == 0 or M % max(res_rows, 1) != 0:
+                    raise NpfkError(f"mlp: residual rows {res_rows} do not tile M={M}")
+            y = torch.empty(M, N, device=x.device, dtype=torch.float32)
+            if M > 0:
+                LIB.call("npfk_linear_fwd", _p(h), ldh, _p(wv), ldw, _p(bv), _p(resv), N, res_rows, _p(y), N, M, N, Kd,
+                         int(out_relu if last else True), mode, st)
+            wvs.append(wv)
+            dims.append((N, Kd, ldh, ldw, res_rows))
+            h, ldh = y, N
+            if not last:
+                acts.append(y)
+        ctx.cfg = (out_relu, x_is_relu, dy_premasked, mode, M, n_layers, dims, res is not None,
+                   None if res is None else res.shape, [wb[2 * i + 1] is not None for i in range(n_layers)], x.shape)
+        ctx.save_for_backward(h if (out_relu and not dy_premasked) else None, *acts, *wvs)
+        return h.reshape(*lead, dims[-1][0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        out_relu, x_is_relu, dy_premasked, mode, M, n_layers, dims, has_res, res_shape, has_b, x_shape = ctx.cfg
+        saved = ctx.saved_tensors
+        y_out, acts, wvs = saved[0], saved[1:1 + n_layers], saved[1 + n_layers:]
+        st = _st()
+        N_out = dims[-1][0]
+        g = _c(dy).reshape(M, N_out)
+        if out_relu and not dy_premasked and M > 0:
+            g2 = torch.empty_like(g)
+            LIB.call("npfk_relu_bwd", _p(g), N_out, _p(y_out), N_out, _p(g2), N_out, M, N_out, st)
+            g = g2
+        dres = None
+        if has_res and ctx.needs_input_grad[4]:
+            res_rows = dims[-1][4]
+            if res_rows == M:
+                dres = g.reshape(res_shape)
+            else:
+                dres = torch.empty(res_shape, device=g.device, dtype=torch.float32)
+                LIB.call("npfk_rows_fold_sum", _p(g), N_out, _p(dres), N_out, res_rows, M // res_rows, N_out, st)
+        grads_wb = [None] * (2 * n_layers)
+        for i in range(n_layers - 1, -1, -1):
+            N, Kd, ldh, ldw, _ = dims[i]
+            hin = acts[i]
+            if ctx.needs_input_grad[5 + 2 * i] or (has_b[i] and ctx.needs_input_grad[6 + 2 * i]):
+                dw = torch.zeros(N, Kd, device=g.device, dtype=torch.float32)
+                db = torch.zeros(N, device=g.device, dtype=torch.float32) if has_b[i] else None
+                if M > 0:
+                    LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(hin), ldh, _p(dw), Kd, _p(db), M, N, Kd, mode, st)
+                grads_wb[2 * i], grads_wb[2 * i + 1] = dw, db
+            need_dx = i > 0 or ctx.needs_input_grad[3]
+            if not need_dx:
+                g = None
+                break
+            masked = i > 0 or x_is_relu
+            dx = torch.empty(M, Kd, device=g.device, dtype=torch.float32)
+            if M > 0:
+                LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wvs[i]), ldw, _p(hin) if masked else None, ldh if masked else 0,
+                         _p(dx), Kd, M, N, Kd, mode, st)
+            g = dx
+        dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[3]) else None
+        return (None, None, None, dx, dres, *grads_wb)
+
+
+def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked=False):
+    """ReLU MLP over `layers` = [(weight, bias), ...] as a single autograd node (see _MlpChainFn)."""
+    flat = []
+    for w, b in layers:
+        flat += [w, b]
+    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, x, res, *flat)
+
+
 # ------------------------------------------------------------------------------------------ broadcast merge
 class _BcastAddReluFn(Function):
     @staticmethod
