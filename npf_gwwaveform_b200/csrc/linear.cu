@@ -247,6 +247,15 @@ int tc_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx, f
                      int64_t M, int N, int K, cudaStream_t st);
 }  // namespace tc
 
+// skinny.cu: streaming kernels for layers with K <= 4 or N <= 4 (return 1 = handled, 0 = not applicable)
+int skinny_linear_fwd(const float* x, int64_t ldx, const float* w, int64_t ldw, const float* bias, const float* res,
+                      int64_t ldres, int64_t res_rows, float* y, int64_t ldy, int64_t M, int N, int K, int relu,
+                      cudaStream_t st);
+int skinny_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw, const float* mask, int64_t ldmask,
+                         float* dx, int64_t lddx, int64_t M, int N, int K, cudaStream_t st);
+int skinny_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx, float* dw, int64_t lddw, float* db,
+                         int64_t M, int N, int K, cudaStream_t st);
+
 __global__ void round_tf32_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t n) {
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
         uint32_t r;
@@ -259,6 +268,15 @@ __global__ void round_tf32_kernel(const float* __restrict__ src, float* __restri
 
 using namespace npfk;
 
+static bool skinny_enabled() {       // NPFK_NO_SKINNY=1 routes the thin layers through the tiled GEMM (debugging)
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("NPFK_NO_SKINNY");
+        v = (e && e[0] == '1') ? 0 : 1;
+    }
+    return v != 0;
+}
+
 extern "C" {
 
 int npfk_linear_fwd(const float* x, int64_t ldx, const float* w, int64_t ldw, const float* bias, const float* res,
@@ -268,6 +286,10 @@ int npfk_linear_fwd(const float* x, int64_t ldx, const float* w, int64_t ldw, co
     NPFK_REQUIRE(M >= 0 && N > 0 && K > 0, "linear_fwd: bad shape M=%lld N=%d K=%d", (long long)M, N, K);
     NPFK_REQUIRE(ldx >= K && ldw >= K && ldy >= N, "linear_fwd: leading dimension too small");
     NPFK_REQUIRE(mode == NPFK_MODE_FP32 || mode == NPFK_MODE_FAST, "linear_fwd: unknown mode %d", mode);
+    if ((K <= 4 || N <= 4) && skinny_enabled()) {
+        const int rc = skinny_linear_fwd(x, ldx, w, ldw, bias, res, ldres, res_rows, y, ldy, M, N, K, relu, as_stream(stream));
+        if (rc != 0) return rc < 0 ? rc : NPFK_OK;
+    }
     if (mode == NPFK_MODE_FAST && tc::nt_eligible(x, ldx, w, ldw, y, ldy, M, N, K, res, ldres, nullptr, 0))
         return tc::tc_linear_fwd(x, ldx, w, ldw, bias, res, ldres, res_rows, y, ldy, M, N, K, relu, /*round_out=*/relu,
                                  as_stream(stream));
@@ -293,6 +315,10 @@ int npfk_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw,
                        float* dx, int64_t lddx, int64_t M, int N, int K, int mode, void* stream) {
     NPFK_REQUIRE(g && w && dx, "linear_bwd_dx: null pointer");
     NPFK_REQUIRE(mode == NPFK_MODE_FP32 || mode == NPFK_MODE_FAST, "linear_bwd_dx: unknown mode %d", mode);
+    if ((K <= 4 || N <= 4) && skinny_enabled()) {
+        const int rc = skinny_linear_bwd_dx(g, ldg, w, ldw, mask, ldmask, dx, lddx, M, N, K, as_stream(stream));
+        if (rc != 0) return rc < 0 ? rc : NPFK_OK;
+    }
     if (mode == NPFK_MODE_FAST && tc::nt_eligible(g, ldg, w, ldw, dx, lddx, M, K, N, nullptr, 0, mask, ldmask))
         return tc::tc_linear_bwd_dx(g, ldg, w, ldw, mask, ldmask, dx, lddx, M, N, K, as_stream(stream));
     GemmArgs a{};
@@ -309,6 +335,10 @@ int npfk_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx,
     NPFK_REQUIRE(g && x && dw, "linear_bwd_dw: null pointer");
     NPFK_REQUIRE(mode == NPFK_MODE_FP32 || mode == NPFK_MODE_FAST, "linear_bwd_dw: unknown mode %d", mode);
     if (M <= 0) return NPFK_OK;
+    if ((K <= 4 || N <= 4) && skinny_enabled()) {
+        const int rc = skinny_linear_bwd_dw(g, ldg, x, ldx, dw, lddw, db, M, N, K, as_stream(stream));
+        if (rc != 0) return rc < 0 ? rc : NPFK_OK;
+    }
     if (mode == NPFK_MODE_FAST && tc::tn_eligible(g, ldg, x, ldx, M, N, K))
         return tc::tc_linear_bwd_dw(g, ldg, x, ldx, dw, lddw, db, M, N, K, as_stream(stream));
     GemmArgs a{};
