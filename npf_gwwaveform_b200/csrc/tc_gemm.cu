@@ -111,7 +111,7 @@ constexpr int kBlockM = 128;        // rows per output tile = UMMA M
 constexpr int kBlockK = 32;         // fp32 elements per 128-byte swizzle row
 constexpr int kABytes = kBlockM * 128;
 constexpr int kStageBytesMax = 227 * 1024;
-constexpr int kEpiBytes = 4 * 2 * 4096;   // per epilogue warp: two 32x32 fp32 staging boxes
+constexpr int kEpiBytes = 4 * 4 * 4096;   // per epilogue warp: two 32x32 fp32 staging boxes + two side-input boxes
 
 struct NtParams {
     int64_t M;            // output rows
@@ -123,6 +123,7 @@ struct NtParams {
     const float* mask;    // dgrad: output is zeroed where mask[m, n] <= 0 (ReLU backward of the layer below)
     int64_t ldmask;
     int relu, round_out;
+    int side_mode;        // 0: none / generic loads, 1: residual via TMA (tmE), 2: mask via TMA (tmE)
     int num_stages, b_bytes;   // smem ring depth, bytes of the B operand per stage
     int* g_abort;
 };
@@ -135,6 +136,7 @@ struct SmemLayout {
     uint64_t* empty;
     uint64_t* tmem_full;
     uint64_t* tmem_empty;
+    uint64_t* side_bar;   // [4 warps][2]
     uint32_t* tmem_ptr;
     volatile int* cta_abort;
 };
@@ -150,13 +152,14 @@ __device__ __forceinline__ SmemLayout carve_smem(uint8_t* raw, int num_stages, i
     s.empty = s.full + num_stages;
     s.tmem_full = s.empty + num_stages;
     s.tmem_empty = s.tmem_full + 2;
-    s.tmem_ptr = reinterpret_cast<uint32_t*>(s.tmem_empty + 2);
+    s.side_bar = s.tmem_empty + 2;
+    s.tmem_ptr = reinterpret_cast<uint32_t*>(s.side_bar + 8);
     s.cta_abort = reinterpret_cast<volatile int*>(s.tmem_ptr + 1);
     return s;
 }
 // bytes of dynamic shared memory for the layout above (plus alignment slack)
 static inline int smem_bytes_for(int num_stages, int stage_bytes, int epi_bytes) {
-    return 1024 + num_stages * stage_bytes + epi_bytes + 1024 + (2 * num_stages + 4) * 8 + 16;
+    return 1024 + num_stages * stage_bytes + epi_bytes + 1024 + (2 * num_stages + 12) * 8 + 16;
 }
 __host__ __device__ inline uint32_t tmem_cols_for(int need) {
     uint32_t c = 32;
@@ -168,7 +171,7 @@ __host__ __device__ inline uint32_t tmem_cols_for(int need) {
 template <bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const __grid_constant__ CUtensorMap tmC, const NtParams p) {
+                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmE, const NtParams p) {
     extern __shared__ uint8_t smem_raw[];
     const int stage_bytes = kABytes + p.b_bytes;
     const SmemLayout sm = carve_smem(smem_raw, p.num_stages, stage_bytes, kEpiBytes);
@@ -192,6 +195,8 @@ tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             mbar_init(&sm.tmem_full[b], 1);
             mbar_init(&sm.tmem_empty[b], 4);
         }
+        for (int b = 0; b < 8; ++b) mbar_init(&sm.side_bar[b], 1);
+        if (p.side_mode) prefetch_tmap(&tmE);
         *sm.cta_abort = 0;
         fence_barrier_init();
     }
@@ -259,8 +264,19 @@ tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     } else {   // ---------------- epilogue warps: TMEM lane quarter = warp % 4
         const int q = warp & 3;
         uint8_t* stg = sm.epi + q * 8192;
+        uint8_t* side = sm.epi + 32768 + q * 8192;          // two 32x32 boxes of the mask / residual, TMA-prefetched
+        uint64_t* sbar = sm.side_bar + q * 2;
         const int64_t res_rows = p.res_rows > 0 ? p.res_rows : p.M;
         uint32_t it = 0, chunk = 0;
+        // side-input box of (tile, column c) -> buffer (chunk index & 1); issued one chunk ahead by lane 0
+        auto side_load = [&](int64_t tile_, int c_, uint32_t chunk_) {
+            const int64_t r0 = tile_ * kBlockM + q * 32;
+            if (r0 < p.M) {
+                mbar_arrive_expect_tx(&sbar[chunk_ & 1], 4096u);
+                tma_load_2d(&tmE, &sbar[chunk_ & 1], side + (chunk_ & 1) * 4096, n0 + c_, (int)r0);
+            }
+        };
+        if (p.side_mode && lane == 0 && (int64_t)blockIdx.x < num_tiles) side_load(blockIdx.x, 0, 0);
         for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
             const uint32_t buf = it & 1, bphase = (it >> 1) & 1;
             bool ok = mbar_wait(&sm.tmem_full[buf], bphase, sm.cta_abort, p.g_abort, 4);
@@ -271,6 +287,10 @@ tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int64_t row = row0 + lane;
             const bool row_ok = row < p.M;
             for (int c = 0; c < Npad; c += 32, ++chunk) {
+                if (p.side_mode && lane == 0) {      // prefetch the next chunk's box (its buffer was read one chunk ago)
+                    if (c + 32 < Npad) side_load(tile, c + 32, chunk + 1);
+                    else if (tile + gridDim.x < num_tiles) side_load(tile + gridDim.x, 0, chunk + 1);
+                }
                 uint32_t v[32];
                 tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)Npad + (uint32_t)c, v);
                 tmem_ld_wait();
@@ -282,7 +302,19 @@ tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 float f[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + sm.bias[c + j];
-                if (p.res != nullptr && row_ok) {
+                const uint8_t* sbox = side + (chunk & 1) * 4096 + lane * 128;
+                if (p.side_mode && row0 < p.M) {
+                    bool sok = mbar_wait(&sbar[chunk & 1], (chunk >> 1) & 1, sm.cta_abort, p.g_abort, 5);
+                    sok = __all_sync(0xffffffffu, sok);
+                    if (!sok) break;
+                }
+                if (p.side_mode == 1 && row0 < p.M) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 r4 = *reinterpret_cast<const float4*>(sbox + ((j ^ (lane & 7)) << 4));
+                        f[4 * j] += r4.x; f[4 * j + 1] += r4.y; f[4 * j + 2] += r4.z; f[4 * j + 3] += r4.w;
+                    }
+                } else if (p.side_mode == 0 && p.res != nullptr && row_ok) {
                     const float* rp = p.res + (row % res_rows) * p.ldres + n0 + c;
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
@@ -295,7 +327,16 @@ tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
                     for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
                 }
-                if (p.mask != nullptr && row_ok) {
+                if (p.side_mode == 2 && row0 < p.M) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 m4 = *reinterpret_cast<const float4*>(sbox + ((j ^ (lane & 7)) << 4));
+                        if (!(m4.x > 0.f)) f[4 * j] = 0.f;
+                        if (!(m4.y > 0.f)) f[4 * j + 1] = 0.f;
+                        if (!(m4.z > 0.f)) f[4 * j + 2] = 0.f;
+                        if (!(m4.w > 0.f)) f[4 * j + 3] = 0.f;
+                    }
+                } else if (p.side_mode == 0 && p.mask != nullptr && row_ok) {
                     const float* mp = p.mask + row * p.ldmask + n0 + c;
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
@@ -515,11 +556,23 @@ static int launch_nt(const float* A, int64_t lda, const float* B, int64_t ldb, f
     if (rc) return rc;
     rc = encode_tmap_2d(&tmC, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 32);
     if (rc) return rc;
+    // mask, or a residual with one row per output row, is prefetched by TMA into the epilogue warps' boxes
+    CUtensorMap tmE = tmC;
+    int side_mode = 0;
+    if (mask && !res) {
+        rc = encode_tmap_2d(&tmE, mask, (uint64_t)N, (uint64_t)M, (uint64_t)ldmask, 32);
+        side_mode = 2;
+    } else if (res && !mask && (res_rows <= 0 || res_rows == M)) {
+        rc = encode_tmap_2d(&tmE, res, (uint64_t)N, (uint64_t)M, (uint64_t)ldres, 32);
+        side_mode = 1;
+    }
+    if (rc) return rc;
     NtParams p{};
     p.M = M; p.N = N; p.K = K;
     p.bias = bias; p.res = res; p.ldres = ldres; p.res_rows = res_rows;
     p.mask = mask; p.ldmask = ldmask;
     p.relu = relu; p.round_out = round_out;
+    p.side_mode = side_mode;
     p.b_bytes = Npad * 128;
     const int stage_bytes = kABytes + p.b_bytes;
     int stages = (kStageBytesMax - 4096 - kEpiBytes) / stage_bytes;
@@ -545,7 +598,7 @@ static int launch_nt(const float* A, int64_t lda, const float* B, int64_t ldb, f
     if (gx < 1) gx = 1;
     if (tiles < gx) gx = (int)tiles;
     dim3 grid((unsigned)gx, (unsigned)n_slices);
-    tc_gemm_nt_kernel<B_MN><<<grid, kThreads, smem, st>>>(tmA, tmB, tmC, p);
+    tc_gemm_nt_kernel<B_MN><<<grid, kThreads, smem, st>>>(tmA, tmB, tmC, tmE, p);
     count_launch();
     return check_launch("tc_gemm_nt");
 }
