@@ -16,7 +16,7 @@
 //                           because the other key tiles of the same task add to the same rows.
 // scale is folded into the dQ / dK drains.  K, Q and dO are each needed K-major and MN-major; tf32 MN-major
 // operands only exist in the 32-byte-atom swizzle, so TMA loads them twice with two tensor maps (L2 hits).
-//   warp 0      TMA producer         warp 1   TMEM allocator + MMA issuer        warps 2..5  softmax / drains
+//   warp 0  TMA producer    warp 1  TMEM allocator + MMA issuer    warps 2..5 / 6..9  two softmax warpgroups (even / odd units)
 #include <math.h>
 
 #include "tc_common.cuh"
@@ -27,7 +27,7 @@ namespace tc {
 constexpr int kBK = 128;                       // keys per CTA (TMEM lanes)
 constexpr int kBQ = 64;                        // queries per half tile (UMMA N of S^T)
 constexpr int kBStages = 3;
-constexpr int kBThreads = 192;
+constexpr int kBThreads = 320;                 // TMA warp, MMA warp, two softmax warpgroups of 4 warps
 constexpr int kBStgBytes = kBK * kBQ * 4;      // 32 KB: dS^T staging, 2 blocks of [128 keys x 32 queries]
 constexpr int kBStgBlock = kBK * 128;          // 16 KB
 constexpr int kBTileQ = kBQ * 128;             // 8 KB: one half tile of a 32-float box
@@ -54,6 +54,7 @@ struct AttnBwdParams {
     int64_t Nq, Nk, Nqp;
     float scale;
     int k_tiles, half_tiles, nsplit, tiles_per_split;
+    int dbg;              // timing experiments only (NPFK_ATTN_DBG): 1 no softmax math, 2 no dQ MMAs, 4 no dV/dK MMAs, 8 no dq red, 16 no staging stores
     int nh;               // UMMA N of the dV / dK / dQ products (16: one head, 32: whole box)
     int* g_abort;
 };
@@ -187,12 +188,18 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && U > 0) {   // ---------------------------------------------------------- MMA issuer
+        if (U > 0 && elect_one()) {   // ------------------------------------------------------- MMA issuer
             const uint32_t idesc_s = make_idesc_tf32(kBQ, false, false);
             const uint32_t idesc_kv = make_idesc_tf32(NH, false, true);    // A from TMEM, B MN-major
             const uint32_t idesc_dq = make_idesc_tf32(NH, true, true);     // A, B MN-major
             const uint32_t kkm = smem_u32(base + kBKkmOff), kmn = smem_u32(base + kBKmnOff), vkm = smem_u32(base + kBVOff);
             const uint32_t stg0 = smem_u32(base + kBStgOff), stage0 = smem_u32(base + kBStageOff);
+            // base descriptors; per-MMA operands are these plus a byte offset (sdesc_advance)
+            const uint64_t d_kkm = make_sdesc_sw128(kkm, 16, 1024), d_vkm = make_sdesc_sw128(vkm, 16, 1024);
+            const uint64_t d_kmn = make_sdesc_mn32(kmn, 16384, 512);
+            const uint64_t d_stage_k = make_sdesc_sw128(stage0, 16, 1024);      // Q / dO half tiles, K-major
+            const uint64_t d_stage_m = make_sdesc_mn32(stage0, 16384, 512);     // Q / dO half tiles, MN-major
+            const uint64_t d_stg = make_sdesc_mn32(stg0, kBStgBlock, 512);
             auto issue_s = [&](int u) -> bool {     // S^T and dP^T of unit u
                 const int i = u / HB, hb = u % HB;
                 const uint32_t st = (uint32_t)i % kBStages;
@@ -200,17 +207,17 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                     if (!mbar_wait(&bar.st_full[st], ((uint32_t)i / kBStages) & 1, cta_abort, p.g_abort, 42)) return false;
                     tc_fence_after();
                 }
-                const uint32_t sa = stage0 + st * kBStageBytes;
                 const uint32_t koff = (uint32_t)(hb * D * 4);
                 const uint32_t tS = tmem_base + (uint32_t)(u & 1) * 128u;
+                const uint64_t dk = sdesc_advance(d_kkm, koff), dv = sdesc_advance(d_vkm, koff);
+                const uint64_t dq = sdesc_advance(d_stage_k, st * kBStageBytes + koff);
+                const uint64_t dd = sdesc_advance(dq, 2 * kBTileQ);
 #pragma unroll
                 for (int s = 0; s < D / 8; ++s)
-                    umma_tf32(tS, make_sdesc_sw128(kkm + koff + s * 32, 16, 1024),
-                              make_sdesc_sw128(sa + koff + s * 32, 16, 1024), idesc_s, s > 0);
+                    umma_tf32(tS, sdesc_advance(dk, s * 32), sdesc_advance(dq, s * 32), idesc_s, s > 0);
 #pragma unroll
                 for (int s = 0; s < D / 8; ++s)
-                    umma_tf32(tS + 64, make_sdesc_sw128(vkm + koff + s * 32, 16, 1024),
-                              make_sdesc_sw128(sa + 2 * kBTileQ + koff + s * 32, 16, 1024), idesc_s, s > 0);
+                    umma_tf32(tS + 64, sdesc_advance(dv, s * 32), sdesc_advance(dd, s * 32), idesc_s, s > 0);
                 umma_commit(&bar.s_full[u & 1]);
                 return true;
             };
@@ -225,23 +232,29 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                     if (!mbar_wait(&bar.p_ready[set], ph, cta_abort, p.g_abort, 44)) return;
                     if (!mbar_wait(&bar.dq_empty[set], ph ^ 1, cta_abort, p.g_abort, 45)) return;
                     tc_fence_after();
-                    const uint32_t sa = stage0 + st * kBStageBytes;
                     const uint32_t tS = tmem_base + set * 128u;
                     const uint32_t hoff = (uint32_t)hb * head_mn_off;
+                    const uint64_t d_do = sdesc_advance(d_stage_m, st * kBStageBytes + 3 * kBTileQ + hoff);
+                    const uint64_t d_q = sdesc_advance(d_stage_m, st * kBStageBytes + kBTileQ + hoff);
+                    const uint64_t d_ds = sdesc_advance(d_stg, set * kBStgBytes);
+                    const uint64_t d_k = sdesc_advance(d_kmn, hoff);
                     const uint32_t acc = tmem_base + kBTmemAcc + (uint32_t)hb * 2u * (uint32_t)NH;
                     const uint32_t first = (i == 0) ? 0u : 1u;
+                    if (!(p.dbg & 4))
 #pragma unroll
                     for (int j = 0; j < kBQ / 8; ++j)      // dV += P^T dO
-                        umma_tf32_ts(acc + NH, tS + 8 * j, make_sdesc_mn32(sa + 3 * kBTileQ + j * 1024 + hoff, 16384, 512),
+                        umma_tf32_ts(acc + NH, tS + 8 * j, sdesc_advance(d_do, j * 1024),
                                      idesc_kv, first | (uint32_t)(j > 0));
+                    if (!(p.dbg & 4))
 #pragma unroll
                     for (int j = 0; j < kBQ / 8; ++j)      // dK += dS^T Q
-                        umma_tf32_ts(acc, tS + 64 + 8 * j, make_sdesc_mn32(sa + kBTileQ + j * 1024 + hoff, 16384, 512),
+                        umma_tf32_ts(acc, tS + 64 + 8 * j, sdesc_advance(d_q, j * 1024),
                                      idesc_kv, first | (uint32_t)(j > 0));
+                    if (!(p.dbg & 2))
 #pragma unroll
                     for (int j = 0; j < kBK / 8; ++j)      // dQ = dS K   (rows 64..127 of the accumulator are unused)
-                        umma_tf32(tmem_base + kBTmemDq + set * 32u, make_sdesc_mn32(stg0 + set * kBStgBytes + j * 1024, kBStgBlock, 512),
-                                  make_sdesc_mn32(kmn + j * 1024 + hoff, 16384, 512), idesc_dq, j > 0);
+                        umma_tf32(tmem_base + kBTmemDq + set * 32u, sdesc_advance(d_ds, j * 1024), sdesc_advance(d_k, j * 1024),
+                                  idesc_dq, j > 0);
                     umma_commit(&bar.dq_full[set]);
                     if (hb == HB - 1) umma_commit(&bar.st_empty[st]);
                 }
@@ -252,6 +265,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
     } else {
         // ------------------------------------------------------------------------------ softmax / drain warps
         const int qd = warp & 3;                       // TMEM lane quarter this warp may access
+        const int wg = (warp - 2) >> 2;                // warpgroup: units of parity wg (= TMEM set, staging buffer, dQ buffer)
         const int kk = qd * 32 + lane;                 // key row inside the tile
         const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
         const float k2 = p.scale * 1.4426950408889634f;
@@ -278,7 +292,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bar.dq_empty[set]);
                 const int64_t q = (int64_t)(ht_begin + i) * kBQ + kk;
-                if (q < p.Nq) {
+                if (q < p.Nq && !(p.dbg & 8)) {
                     float* dst = p.dq + ((int64_t)b * p.Nq + q) * p.E + box * 32 + hb * D;
 #pragma unroll
                     for (int d4 = 0; d4 < D / 4; ++d4)
@@ -289,18 +303,20 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
             return true;
         };
         auto role = [&]() {
-            for (int u = 0; u < U; ++u) {
+            int last = -1;
+            for (int u = wg; u < U; u += 2) {
                 const int i = u / HB, hb = u % HB;
                 const uint32_t set = (uint32_t)u & 1, st = (uint32_t)i % kBStages;
                 if (u >= 2 && !drain_dq(u - 2)) return;          // also frees staging[set]
-                if (hb == 0 && !wait_all(&bar.st_full[st], ((uint32_t)i / kBStages) & 1, 52)) return;
+                last = u;
+                if (!wait_all(&bar.st_full[st], ((uint32_t)i / kBStages) & 1, 52)) return;
                 if (!wait_all(&bar.s_full[set], ((uint32_t)u >> 1) & 1, 53)) return;
                 tc_fence_after();
                 const uint8_t* stats = base + kBStageOff + st * kBStageBytes + 4 * kBTileQ + hb * 512;
                 uint8_t* stg = base + kBStgOff + set * kBStgBytes + kk * 128;
                 const uint32_t tS = lane_base + set * 128u;
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {                    // 32 queries at a time
+                for (int c = 0; c < ((p.dbg & 1) ? 0 : 2); ++c) {                    // 32 queries at a time
                     uint32_t s[32], g[32];
                     tmem_ld_32x32(tS + c * 32, s);
                     tmem_ld_32x32(tS + 64 + c * 32, g);
@@ -324,13 +340,18 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                     tmem_st_32x32(tS + 64 + c * 32, g);
                     // dS^T row of this key into the MN-major staging block c: 32-byte chunk ch at (ch ^ (kk & 3))
                     uint8_t* blk = stg + c * kBStgBlock;
+                    if (!(p.dbg & 16))
 #pragma unroll
-                    for (int t = 0; t < 8; ++t) {
-                        const uint32_t ch = (uint32_t)t >> 1, half = ((uint32_t)t & 1) ^ hsel;
-                        const int j = (int)(ch * 8 + half * 4);
-                        *reinterpret_cast<float4*>(blk + ((ch ^ sw) << 5) + (half << 4)) =
-                            make_float4(__uint_as_float(g[j]), __uint_as_float(g[j + 1]), __uint_as_float(g[j + 2]),
-                                        __uint_as_float(g[j + 3]));
+                    for (int ch = 0; ch < 4; ++ch) {
+                        // both 16-byte halves of chunk ch; lanes with hsel store the upper half first (conflict-free),
+                        // chosen with selects so that g[] keeps static register indices
+                        const float4 lo = make_float4(__uint_as_float(g[8 * ch]), __uint_as_float(g[8 * ch + 1]),
+                                                      __uint_as_float(g[8 * ch + 2]), __uint_as_float(g[8 * ch + 3]));
+                        const float4 hi = make_float4(__uint_as_float(g[8 * ch + 4]), __uint_as_float(g[8 * ch + 5]),
+                                                      __uint_as_float(g[8 * ch + 6]), __uint_as_float(g[8 * ch + 7]));
+                        uint8_t* dst = blk + (((uint32_t)ch ^ sw) << 5);
+                        *reinterpret_cast<float4*>(dst + (hsel << 4)) = hsel ? hi : lo;
+                        *reinterpret_cast<float4*>(dst + ((hsel ^ 1u) << 4)) = hsel ? lo : hi;
                     }
                 }
                 tmem_st_wait();
@@ -339,14 +360,13 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bar.p_ready[set]);
             }
-            for (int u = max(0, U - 2); u < U; ++u)
-                if (!drain_dq(u)) return;
+            if (last >= 0 && !drain_dq(last)) return;
             // ---- dK / dV of this key tile
             if (!wait_all(bar.fin, 0, 54)) return;
             tc_fence_after();
             const int64_t key = (int64_t)kt * kBK + kk;
 #pragma unroll
-            for (int hb = 0; hb < HB; ++hb) {
+            for (int hb = wg; hb < HB; hb += 2) {           // warpgroup g drains head g of the box
                 uint32_t rk[D], rv[D];
                 const uint32_t acc = lane_base + kBTmemAcc + (uint32_t)hb * 2u * (uint32_t)NH + (uint32_t)hb * head_col;
                 if constexpr (D == 16) {
@@ -431,6 +451,12 @@ int attn_bwd_tc(const float* q, const float* k, const float* v, const float* out
         const char* e = getenv("NPFK_ATTN_BWD_NH");
         nh_env = e ? atoi(e) : 0;
     }
+    static int dbg_env = -1;
+    if (dbg_env < 0) {
+        const char* e = getenv("NPFK_ATTN_DBG");
+        dbg_env = e ? atoi(e) : 0;
+    }
+    p.dbg = dbg_env;
     p.nh = (D == 16) ? ((nh_env == 32) ? 32 : 16) : 32;
     p.g_abort = abort_flag_ptr();
 

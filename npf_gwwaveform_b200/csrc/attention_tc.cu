@@ -153,11 +153,16 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {   // -------------------------------------------------------------------- MMA issuer
+        if (elect_one()) {   // ------------------------------------------------------------------ MMA issuer
             const uint32_t idesc_s = make_idesc_tf32(kAKC, false, false);
             const uint32_t idesc_pv = make_idesc_tf32(32, false, true);
             const uint32_t ring_addr = smem_u32(base + kARingOff);
             const uint32_t p_addr0 = smem_u32(base + kAPOff);
+            // base descriptors: per-MMA operands are these plus a byte offset (one add each)
+            const uint64_t d_ring_k = make_sdesc_sw128(ring_addr, 16, 1024);
+            const uint64_t d_ring_v = make_sdesc_mn32(ring_addr + kAKBytes, 4096, 512);
+            const uint64_t d_q0 = make_sdesc_sw128(smem_u32(base + kAQOff), 16, 1024);
+            const uint64_t d_p0 = make_sdesc_sw128(p_addr0, 16, 1024);
             uint32_t s_it = 0, p_it = 0, o_it = 0, kv_it = 0;
             auto role = [&]() {
                 for (int qt = qt_begin; qt < qt_end; ++qt) {
@@ -165,7 +170,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     const uint32_t qb = qi & 1, qph = (qi >> 1) & 1;
                     if (!mbar_wait(&bar.q_full[qb], qph, cta_abort, p.g_abort, 23)) return;
                     tc_fence_after();
-                    const uint32_t q_addr = smem_u32(base + kAQOff + qb * kAQBytes);
+                    const uint64_t d_q = sdesc_advance(d_q0, qb * kAQBytes);
                     for (int hb = 0; hb < HB; ++hb) {
                         const uint32_t koff = (uint32_t)(hb * D * 4);
                         // S = Q_h K_h^T for chunk c into S buffer (s_it & 1); returns the ring slot used
@@ -176,11 +181,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                             const uint32_t sb = s_it & 1;
                             if (!mbar_wait(&bar.s_empty[sb], ((s_it >> 1) & 1) ^ 1, cta_abort, p.g_abort, 25)) return false;
                             tc_fence_after();
-                            const uint32_t k_addr = ring_addr + slot * kASlotBytes;
+                            const uint64_t dq = sdesc_advance(d_q, koff), dk = sdesc_advance(d_ring_k, slot * kASlotBytes + koff);
 #pragma unroll
                             for (int s = 0; s < D / 8; ++s)
-                                umma_tf32(tmem_base + sb * kAKC, make_sdesc_sw128(q_addr + koff + s * 32, 16, 1024),
-                                          make_sdesc_sw128(k_addr + koff + s * 32, 16, 1024), idesc_s, s > 0);
+                                umma_tf32(tmem_base + sb * kAKC, sdesc_advance(dq, s * 32), sdesc_advance(dk, s * 32), idesc_s, s > 0);
                             umma_commit(&bar.s_full[sb]);
                             ++s_it;
                             return true;
@@ -204,13 +208,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                             if (!mbar_wait(&bar.p_full[pb], (p_it >> 1) & 1, cta_abort, p.g_abort, 27)) return;
                             tc_fence_after();
                             const uint32_t slot = resident ? (uint32_t)c : kv_it % kARing;
-                            const uint32_t v_addr = ring_addr + slot * kASlotBytes + kAKBytes;
-                            const uint32_t p_addr = p_addr0 + pb * kAPBytes;
+                            const uint64_t dv = sdesc_advance(d_ring_v, slot * kASlotBytes);
+                            const uint64_t dp = sdesc_advance(d_p0, pb * kAPBytes);
 #pragma unroll
                             for (int j = 0; j < kAKC / 8; ++j)
                                 umma_tf32(tmem_base + kATmemO + ob * 32,
-                                          make_sdesc_sw128(p_addr + (j >> 2) * (kAQT * 128) + (j & 3) * 32, 16, 1024),
-                                          make_sdesc_mn32(v_addr + j * 1024, 4096, 512), idesc_pv, (c | j) != 0);
+                                          sdesc_advance(dp, (j >> 2) * (kAQT * 128) + (j & 3) * 32),
+                                          sdesc_advance(dv, j * 1024), idesc_pv, (c | j) != 0);
                             umma_commit(&bar.p_empty[pb]);
                             ++p_it;
                             if (!resident) {

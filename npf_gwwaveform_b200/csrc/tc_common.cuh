@@ -178,6 +178,23 @@ __device__ __forceinline__ uint64_t make_sdesc_mn32(uint32_t smem_addr, uint32_t
     return make_sdesc(smem_addr, lbo_bytes, sbo_bytes, 1u);
 }
 
+// A descriptor for (smem_addr + byte_off) is the base descriptor plus byte_off >> 4 (the start-address field is the
+// low 14 bits and shared memory ends below 2^18 bytes), so per-MMA descriptor updates are a single add.
+__device__ __forceinline__ uint64_t sdesc_advance(uint64_t desc, uint32_t byte_off) { return desc + (uint64_t)(byte_off >> 4); }
+
+// one elected lane of a converged warp (lets ptxas issue tcgen05.mma without a per-lane election loop)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // 32 lanes x 32 columns of fp32: thread t of the warp receives row (lane base + t), 32 consecutive columns
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(

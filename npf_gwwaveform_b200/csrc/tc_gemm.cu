@@ -232,8 +232,11 @@ tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {   // ---------------- MMA issuer
+        if (elect_one()) {   // ---------------- MMA issuer
             const uint32_t idesc = make_idesc_tf32(Nc, false, B_MN);
+            const uint32_t stage0 = smem_u32(sm.stages);
+            const uint64_t d_a0 = make_sdesc_sw128(stage0, 16, 1024);
+            const uint64_t d_b0 = B_MN ? make_sdesc_mn32(stage0 + kABytes, 4096, 512) : make_sdesc_sw128(stage0 + kABytes, 16, 1024);
             int stage = 0;
             uint32_t phase = 0;
             uint32_t it = 0;
@@ -246,15 +249,12 @@ tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 for (int kb = 0; kb < KB; ++kb) {
                     if (!mbar_wait(&sm.full[stage], phase, sm.cta_abort, p.g_abort, 3)) { alive = false; break; }
                     tc_fence_after();
-                    const uint32_t a_addr = smem_u32(sm.stages + (size_t)stage * stage_bytes);
-                    const uint32_t b_addr = a_addr + kABytes;
+                    const uint32_t soff = (uint32_t)stage * (uint32_t)stage_bytes;
+                    const uint64_t ad0 = sdesc_advance(d_a0, soff), bd0 = sdesc_advance(d_b0, soff);
 #pragma unroll
-                    for (int s = 0; s < 4; ++s) {
-                        const uint64_t ad = make_sdesc_sw128(a_addr + s * 32, 16, 1024);
-                        const uint64_t bd = B_MN ? make_sdesc_mn32(b_addr + s * 1024, 4096, 512)
-                                                 : make_sdesc_sw128(b_addr + s * 32, 16, 1024);
-                        umma_tf32(d, ad, bd, idesc, (kb | s) != 0);
-                    }
+                    for (int s = 0; s < 4; ++s)
+                        umma_tf32(d, sdesc_advance(ad0, s * 32), sdesc_advance(bd0, B_MN ? s * 1024 : s * 32), idesc,
+                                  (kb | s) != 0);
                     umma_commit(&sm.empty[stage]);
                     if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
                 }
@@ -445,22 +445,22 @@ tc_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {   // ---------------- MMA issuer
+        if (elect_one()) {   // ---------------- MMA issuer
             const uint32_t idesc = make_idesc_tf32(Kn, true, true);
+            const uint32_t stage0 = smem_u32(sm.stages);
+            const uint64_t d_a0 = make_sdesc_mn32(stage0, 4096, 512), d_b0 = make_sdesc_mn32(stage0 + kABytes, 4096, 512);
             int stage = 0;
             uint32_t phase = 0;
             bool alive = true;
             for (int64_t kb = kb_begin; kb < kb_end; ++kb) {
                 if (!mbar_wait(&sm.full[stage], phase, sm.cta_abort, p.g_abort, 13)) { alive = false; break; }
                 tc_fence_after();
-                const uint32_t a_addr = smem_u32(sm.stages + (size_t)stage * stage_bytes);
-                const uint32_t b_addr = a_addr + kABytes;
+                const uint32_t soff = (uint32_t)stage * (uint32_t)stage_bytes;
+                const uint64_t ad0 = sdesc_advance(d_a0, soff), bd0 = sdesc_advance(d_b0, soff);
 #pragma unroll
-                for (int s = 0; s < 4; ++s) {
-                    const uint64_t ad = make_sdesc_mn32(a_addr + s * 1024, 4096, 512);
-                    const uint64_t bd = make_sdesc_mn32(b_addr + s * 1024, 4096, 512);
-                    umma_tf32(tmem_base, ad, bd, idesc, (kb > kb_begin || s > 0) ? 1u : 0u);
-                }
+                for (int s = 0; s < 4; ++s)
+                    umma_tf32(tmem_base, sdesc_advance(ad0, s * 1024), sdesc_advance(bd0, s * 1024), idesc,
+                              (kb > kb_begin || s > 0) ? 1u : 0u);
                 umma_commit(&sm.empty[stage]);
                 if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
             }
