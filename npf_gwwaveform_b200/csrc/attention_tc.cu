@@ -6,13 +6,15 @@
 // byte offset inside the swizzled row, so no permute copies and no [B*H, Nq, Nk] logits ever reach HBM.
 //
 // One CTA owns (batch item, column box) and walks query tiles of 128 rows.  K/V of the box stay resident in
-// shared memory when the context fits the ring (<= 512 points), otherwise they are streamed per pass.
-//   warp 0      TMA producer (Q tiles, K/V chunks of 64 keys)
-//   warp 1      TMEM allocator + tcgen05.mma issuer (one thread)
-//   warps 2..5  softmax: thread = query row (TMEM lane), tcgen05.ld of the logits, exp2, P to swizzled smem
-// Forward per (query tile, head):  pass 1  S = Q K^T per chunk -> running row maximum (no exponentials);
-//                                  pass 2  S again -> P = exp2((S - max) * scale*log2e) -> O += P V in TMEM.
-// Recomputing S (2 tiny MMAs per chunk) is cheaper than rescaling O in TMEM when the maximum moves.
+// shared memory when the context fits the ring (<= 512 points), otherwise they are streamed once per unit pair.
+// A unit is (query tile, head); units 2i and 2i+1 run concurrently on two softmax warpgroups:
+//   warp 0            TMA producer (Q tiles, K/V chunks of 64 keys)
+//   warp 1            TMEM allocator + tcgen05.mma issuer (one elected thread)
+//   warps 2..5, 6..9  softmax warpgroups: thread = query row (TMEM lane)
+// Per (unit, chunk):  S = Q_h K_c^T (TMEM)  ->  online softmax in registers: running max m, P = exp2((S-m)*scale*log2e)
+// truncated to tf32 and written back IN PLACE over S (tcgen05.st)  ->  O_c = P V_c with A = P read from TMEM  ->
+// the warpgroup folds O_c into its register accumulator, rescaled by exp2((m_old-m_new)*scale*log2e).
+// Single pass: every logit is computed and read once; nothing but q, k, v, out and lse touches HBM.
 #include <math.h>
 
 #include "tc_common.cuh"
@@ -23,18 +25,18 @@ namespace tc {
 constexpr int kAQT = 128;                    // queries per tile (UMMA M, TMEM lanes)
 constexpr int kAKC = 64;                     // keys per chunk (UMMA N of S, K of PV)
 constexpr int kARing = 8;                    // K/V ring slots
-constexpr int kAThreads = 192;
+constexpr int kAQSlots = 4;                  // Q tile slots
+constexpr int kAThreads = 320;
 constexpr int kAKBytes = kAKC * 128;         // one chunk of a 32-float box
 constexpr int kASlotBytes = 2 * kAKBytes;    // K chunk + V chunk
 constexpr int kAQBytes = kAQT * 128;
-constexpr int kAPBytes = kAQT * kAKC * 4;
 constexpr int kARingOff = 0;
 constexpr int kAQOff = kARing * kASlotBytes;             // 131072
-constexpr int kAPOff = kAQOff + 2 * kAQBytes;            // 163840
-constexpr int kABarOff = kAPOff + 2 * kAPBytes;          // 229376
-constexpr int kANumBars = 2 * kARing + 20;
+constexpr int kABarOff = kAQOff + kAQSlots * kAQBytes;   // 196608
+constexpr int kANumBars = 2 * kARing + 2 * kAQSlots + 12;
 constexpr int kAFwdSmem = 1024 + kABarOff + kANumBars * 8 + 16;
-constexpr uint32_t kATmemCols = 256;         // S: 2 x 64 columns, O: 2 x 32 columns
+constexpr uint32_t kATmemCols = 512;         // per warpgroup: S 2 x 64 columns, O 2 x 32 columns (192), two warpgroups
+constexpr uint32_t kATmemWg = 192;
 constexpr uint32_t kATmemO = 128;
 
 struct AttnParams {
@@ -48,16 +50,13 @@ struct AttnParams {
 };
 
 struct AttnBars {
-    uint64_t* kv_full;
-    uint64_t* kv_empty;
-    uint64_t* q_full;
-    uint64_t* q_empty;
-    uint64_t* s_full;
-    uint64_t* s_empty;
-    uint64_t* p_full;
-    uint64_t* p_empty;
-    uint64_t* o_full;
-    uint64_t* o_empty;
+    uint64_t* kv_full;    // [kARing]
+    uint64_t* kv_empty;   // [kARing]
+    uint64_t* q_full;     // [kAQSlots]
+    uint64_t* q_empty;    // [kAQSlots]
+    uint64_t* s_full;     // [2 warpgroups][2 buffers]
+    uint64_t* p_ready;    // [2][2]
+    uint64_t* o_full;     // [2][2]
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -78,13 +77,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     bar.kv_full = bars;
     bar.kv_empty = bars + kARing;
     bar.q_full = bars + 2 * kARing;
-    bar.q_empty = bar.q_full + 2;
-    bar.s_full = bar.q_full + 4;
-    bar.s_empty = bar.q_full + 6;
-    bar.p_full = bar.q_full + 8;
-    bar.p_empty = bar.q_full + 10;
-    bar.o_full = bar.q_full + 12;
-    bar.o_empty = bar.q_full + 14;
+    bar.q_empty = bar.q_full + kAQSlots;
+    bar.s_full = bar.q_empty + kAQSlots;
+    bar.p_ready = bar.s_full + 4;
+    bar.o_full = bar.s_full + 8;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + kANumBars);
     volatile int* cta_abort = reinterpret_cast<volatile int*>(tmem_ptr + 1);
 
@@ -94,6 +90,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int b = item / boxes, box = item % boxes;
     const int qt_begin = split * p.tiles_per_split;
     const int qt_end = min(p.q_tiles, qt_begin + p.tiles_per_split);
+    const int n_qt = max(qt_end - qt_begin, 0);
+    const int U = n_qt * HB;                 // units = (query tile, head); unit u -> tile u / HB, head u % HB
     const int nc = p.n_chunks;
     const bool resident = nc <= kARing;
 
@@ -105,15 +103,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             mbar_init(&bar.kv_full[i], 1);
             mbar_init(&bar.kv_empty[i], 1);
         }
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < kAQSlots; ++i) {
             mbar_init(&bar.q_full[i], 1);
             mbar_init(&bar.q_empty[i], 1);
+        }
+        for (int i = 0; i < 4; ++i) {
             mbar_init(&bar.s_full[i], 1);
-            mbar_init(&bar.s_empty[i], 4);
-            mbar_init(&bar.p_full[i], 4);
-            mbar_init(&bar.p_empty[i], 1);
+            mbar_init(&bar.p_ready[i], 4);
             mbar_init(&bar.o_full[i], 1);
-            mbar_init(&bar.o_empty[i], 4);
         }
         *cta_abort = 0;
         fence_barrier_init();
@@ -123,9 +120,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    const int n_pairs = (U + 1) / 2;
 
     if (warp == 0) {
-        if (lane == 0 && qt_begin < qt_end) {   // ------------------------------------------------ TMA producer
+        if (lane == 0 && U > 0) {   // ------------------------------------------------------------ TMA producer
             auto load_kv = [&](int slot, int c) {
                 uint8_t* sK = base + kARingOff + slot * kASlotBytes;
                 mbar_arrive_expect_tx(&bar.kv_full[slot], (uint32_t)kASlotBytes);
@@ -135,214 +133,193 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             if (resident)
                 for (int c = 0; c < nc; ++c) load_kv(c, c);
             uint32_t kv_it = 0;
+            int next_tile = 0;      // local index of the next Q tile to load
             bool alive = true;
-            for (int qt = qt_begin; qt < qt_end && alive; ++qt) {
-                const uint32_t qi = (uint32_t)(qt - qt_begin);
-                const uint32_t qb = qi & 1, qph = (qi >> 1) & 1;
-                if (!mbar_wait(&bar.q_empty[qb], qph ^ 1, cta_abort, p.g_abort, 21)) break;
-                mbar_arrive_expect_tx(&bar.q_full[qb], (uint32_t)kAQBytes);
-                tma_load_3d(&tmQ, &bar.q_full[qb], base + kAQOff + qb * kAQBytes, box * 32, qt * kAQT, b);
-                if (!resident) {
-                    for (int rep = 0; rep < 2 * HB && alive; ++rep)
-                        for (int c = 0; c < nc; ++c, ++kv_it) {
-                            const uint32_t slot = kv_it % kARing, ph = (kv_it / kARing) & 1;
-                            if (!mbar_wait(&bar.kv_empty[slot], ph ^ 1, cta_abort, p.g_abort, 22)) { alive = false; break; }
-                            load_kv((int)slot, c);
-                        }
+            for (int pi = 0; pi < n_pairs && alive; ++pi) {
+                const int last_tile = min(2 * pi + 1, U - 1) / HB;      // tiles used by units 2pi, 2pi+1
+                for (; next_tile <= last_tile; ++next_tile) {
+                    const uint32_t qs = (uint32_t)next_tile % kAQSlots, qph = ((uint32_t)next_tile / kAQSlots) & 1;
+                    if (!mbar_wait(&bar.q_empty[qs], qph ^ 1, cta_abort, p.g_abort, 21)) { alive = false; break; }
+                    mbar_arrive_expect_tx(&bar.q_full[qs], (uint32_t)kAQBytes);
+                    tma_load_3d(&tmQ, &bar.q_full[qs], base + kAQOff + qs * kAQBytes, box * 32, (qt_begin + next_tile) * kAQT, b);
+                }
+                if (!resident && alive) {
+                    for (int c = 0; c < nc; ++c, ++kv_it) {
+                        const uint32_t slot = kv_it % kARing, ph = (kv_it / kARing) & 1;
+                        if (!mbar_wait(&bar.kv_empty[slot], ph ^ 1, cta_abort, p.g_abort, 22)) { alive = false; break; }
+                        load_kv((int)slot, c);
+                    }
                 }
             }
         }
     } else if (warp == 1) {
-        if (elect_one()) {   // ------------------------------------------------------------------ MMA issuer
+        if (U > 0 && elect_one()) {   // ---------------------------------------------------------- MMA issuer
             const uint32_t idesc_s = make_idesc_tf32(kAKC, false, false);
-            const uint32_t idesc_pv = make_idesc_tf32(32, false, true);
+            const uint32_t idesc_pv = make_idesc_tf32(D, false, true);          // A = P from TMEM, B = V MN-major
             const uint32_t ring_addr = smem_u32(base + kARingOff);
-            const uint32_t p_addr0 = smem_u32(base + kAPOff);
-            // base descriptors: per-MMA operands are these plus a byte offset (one add each)
             const uint64_t d_ring_k = make_sdesc_sw128(ring_addr, 16, 1024);
             const uint64_t d_ring_v = make_sdesc_mn32(ring_addr + kAKBytes, 4096, 512);
             const uint64_t d_q0 = make_sdesc_sw128(smem_u32(base + kAQOff), 16, 1024);
-            const uint64_t d_p0 = make_sdesc_sw128(p_addr0, 16, 1024);
-            uint32_t s_it = 0, p_it = 0, o_it = 0, kv_it = 0;
+            uint32_t cnt[2] = {0, 0};       // S / P / O buffer use counters per warpgroup
+            uint32_t kv_it = 0;             // streamed K/V chunks consumed so far
             auto role = [&]() {
-                for (int qt = qt_begin; qt < qt_end; ++qt) {
-                    const uint32_t qi = (uint32_t)(qt - qt_begin);
-                    const uint32_t qb = qi & 1, qph = (qi >> 1) & 1;
-                    if (!mbar_wait(&bar.q_full[qb], qph, cta_abort, p.g_abort, 23)) return;
+                for (int pi = 0; pi < n_pairs; ++pi) {
+                    const int ng = min(2, U - 2 * pi);
+                    uint64_t dq[2];
+                    uint32_t koff[2], voff[2];
+                    for (int g = 0; g < ng; ++g) {
+                        const int u = 2 * pi + g, t = u / HB, hb = u % HB;
+                        const uint32_t qs = (uint32_t)t % kAQSlots;
+                        if (HB == 1 || g == 0) {
+                            if (!mbar_wait(&bar.q_full[qs], ((uint32_t)t / kAQSlots) & 1, cta_abort, p.g_abort, 23)) return;
+                        }
+                        koff[g] = (uint32_t)(hb * D * 4);
+                        voff[g] = (D == 16) ? (uint32_t)hb * 64u : 0u;
+                        dq[g] = sdesc_advance(d_q0, qs * kAQBytes + koff[g]);
+                    }
                     tc_fence_after();
-                    const uint64_t d_q = sdesc_advance(d_q0, qb * kAQBytes);
-                    for (int hb = 0; hb < HB; ++hb) {
-                        const uint32_t koff = (uint32_t)(hb * D * 4);
-                        // S = Q_h K_h^T for chunk c into S buffer (s_it & 1); returns the ring slot used
-                        auto issue_s = [&](int c, uint32_t kvi) -> bool {
-                            const uint32_t slot = resident ? (uint32_t)c : kvi % kARing;
-                            const uint32_t ph = resident ? 0u : (kvi / kARing) & 1;
-                            if (!mbar_wait(&bar.kv_full[slot], ph, cta_abort, p.g_abort, 24)) return false;
-                            const uint32_t sb = s_it & 1;
-                            if (!mbar_wait(&bar.s_empty[sb], ((s_it >> 1) & 1) ^ 1, cta_abort, p.g_abort, 25)) return false;
-                            tc_fence_after();
-                            const uint64_t dq = sdesc_advance(d_q, koff), dk = sdesc_advance(d_ring_k, slot * kASlotBytes + koff);
+                    // S(g, c) = Q_g K_c^T into S buffer (cnt[g] + c) & 1 of warpgroup g
+                    auto issue_s = [&](int c) -> bool {
+                        const uint32_t slot = resident ? (uint32_t)c : (kv_it + (uint32_t)c) % kARing;
+                        const uint32_t ph = resident ? 0u : ((kv_it + (uint32_t)c) / kARing) & 1;
+                        if (!mbar_wait(&bar.kv_full[slot], ph, cta_abort, p.g_abort, 24)) return false;
+                        tc_fence_after();
+                        for (int g = 0; g < ng; ++g) {
+                            const uint32_t n = cnt[g] + (uint32_t)c, sb = n & 1;
+                            const uint64_t dk = sdesc_advance(d_ring_k, slot * kASlotBytes + koff[g]);
+                            const uint32_t tS = tmem_base + (uint32_t)g * kATmemWg + sb * kAKC;
 #pragma unroll
                             for (int s = 0; s < D / 8; ++s)
-                                umma_tf32(tmem_base + sb * kAKC, sdesc_advance(dq, s * 32), sdesc_advance(dk, s * 32), idesc_s, s > 0);
-                            umma_commit(&bar.s_full[sb]);
-                            ++s_it;
-                            return true;
-                        };
-                        // pass 1: row maxima
-                        for (int c = 0; c < nc; ++c) {
-                            if (!issue_s(c, kv_it)) return;
-                            if (!resident) {
-                                umma_commit(&bar.kv_empty[kv_it % kARing]);
-                                ++kv_it;
-                            }
+                                umma_tf32(tS, sdesc_advance(dq[g], s * 32), sdesc_advance(dk, s * 32), idesc_s, s > 0);
+                            umma_commit(&bar.s_full[g * 2 + sb]);
                         }
-                        // pass 2: P V
-                        const uint32_t ob = o_it & 1;
-                        if (!mbar_wait(&bar.o_empty[ob], ((o_it >> 1) & 1) ^ 1, cta_abort, p.g_abort, 26)) return;
-                        tc_fence_after();
-                        if (!issue_s(0, kv_it)) return;
-                        for (int c = 0; c < nc; ++c) {
-                            if (c + 1 < nc && !issue_s(c + 1, kv_it + 1)) return;
-                            const uint32_t pb = p_it & 1;
-                            if (!mbar_wait(&bar.p_full[pb], (p_it >> 1) & 1, cta_abort, p.g_abort, 27)) return;
+                        return true;
+                    };
+                    if (!issue_s(0)) return;
+                    for (int c = 0; c < nc; ++c) {
+                        if (c + 1 < nc && !issue_s(c + 1)) return;
+                        const uint32_t slot = resident ? (uint32_t)c : (kv_it + (uint32_t)c) % kARing;
+                        for (int g = 0; g < ng; ++g) {
+                            const uint32_t n = cnt[g] + (uint32_t)c, sb = n & 1;
+                            if (!mbar_wait(&bar.p_ready[g * 2 + sb], (n >> 1) & 1, cta_abort, p.g_abort, 27)) return;
                             tc_fence_after();
-                            const uint32_t slot = resident ? (uint32_t)c : kv_it % kARing;
-                            const uint64_t dv = sdesc_advance(d_ring_v, slot * kASlotBytes);
-                            const uint64_t dp = sdesc_advance(d_p0, pb * kAPBytes);
+                            const uint32_t tP = tmem_base + (uint32_t)g * kATmemWg + sb * kAKC;
+                            const uint32_t tO = tmem_base + (uint32_t)g * kATmemWg + kATmemO + sb * 32;
+                            const uint64_t dv = sdesc_advance(d_ring_v, slot * kASlotBytes + voff[g]);
 #pragma unroll
                             for (int j = 0; j < kAKC / 8; ++j)
-                                umma_tf32(tmem_base + kATmemO + ob * 32,
-                                          sdesc_advance(dp, (j >> 2) * (kAQT * 128) + (j & 3) * 32),
-                                          sdesc_advance(dv, j * 1024), idesc_pv, (c | j) != 0);
-                            umma_commit(&bar.p_empty[pb]);
-                            ++p_it;
-                            if (!resident) {
-                                umma_commit(&bar.kv_empty[slot]);
-                                ++kv_it;
-                            }
+                                umma_tf32_ts(tO, tP + 8 * j, sdesc_advance(dv, j * 1024), idesc_pv, j > 0);
+                            umma_commit(&bar.o_full[g * 2 + sb]);
                         }
-                        umma_commit(&bar.o_full[ob]);
-                        ++o_it;
+                        if (!resident) umma_commit(&bar.kv_empty[slot]);
                     }
-                    umma_commit(&bar.q_empty[qb]);
+                    if (!resident) kv_it += (uint32_t)nc;
+                    for (int g = 0; g < ng; ++g) {
+                        cnt[g] += (uint32_t)nc;
+                        const int u = 2 * pi + g, t = u / HB;
+                        if (HB == 1 || g == ng - 1) umma_commit(&bar.q_empty[(uint32_t)t % kAQSlots]);
+                    }
                 }
             };
             role();
         }
-    } else {   // ---------------------------------------------------------------------------- softmax warps
-        const int qd = warp & 3;
+    } else {
+        // ------------------------------------------------------------------------------ softmax warpgroups
+        const int qd = warp & 3;                       // TMEM lane quarter of this warp
+        const int wg = (warp - 2) >> 2;                // warpgroup = unit parity
         const int row = qd * 32 + lane;
-        const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+        const uint32_t wg_base = tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)wg * kATmemWg;
         const float k2 = p.scale * 1.4426950408889634f;
-        uint32_t s_it = 0, p_it = 0, o_it = 0;
+        const int tail_valid = (int)(p.Nk - (int64_t)(nc - 1) * kAKC);      // valid keys in the last chunk (1..64)
+        uint32_t cnt = 0;
         auto wait_all = [&](uint64_t* bb, uint32_t ph, int code) -> bool {
             bool ok = mbar_wait(bb, ph, cta_abort, p.g_abort, code);
             return __all_sync(0xffffffffu, ok);
         };
         auto role = [&]() {
-            for (int qt = qt_begin; qt < qt_end; ++qt) {
-                const int64_t qrow = (int64_t)qt * kAQT + row;
-                for (int hb = 0; hb < HB; ++hb) {
-                    // ---- pass 1: running maximum of the raw logits
-                    float m = -INFINITY;
-                    for (int c = 0; c < nc; ++c) {
-                        const uint32_t sb = s_it & 1;
-                        if (!wait_all(&bar.s_full[sb], (s_it >> 1) & 1, 31)) return;
-                        tc_fence_after();
-                        const int64_t key0 = (int64_t)c * kAKC;
+            for (int u = wg; u < U; u += 2) {
+                const int t = u / HB, hb = u % HB;
+                const int64_t qrow = (int64_t)(qt_begin + t) * kAQT + row;
+                float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
+                float o[D];
 #pragma unroll
-                        for (int half = 0; half < 2; ++half) {
-                            uint32_t v[32];
-                            tmem_ld_32x32(lane_base + sb * kAKC + half * 32, v);
-                            tmem_ld_wait();
-                            if (key0 + half * 32 + 32 <= p.Nk) {
+                for (int d = 0; d < D; ++d) o[d] = 0.f;
+                // fold O_c of buffer use n into the accumulator: o = o * alpha + O_c
+                auto fold = [&](uint32_t n, float alpha) -> bool {
+                    if (!wait_all(&bar.o_full[wg * 2 + (n & 1)], (n >> 1) & 1, 34)) return false;
+                    tc_fence_after();
+                    uint32_t r[D];
+                    if constexpr (D == 16) tmem_ld_32x16(wg_base + kATmemO + (n & 1) * 32, r);
+                    else tmem_ld_32x32(wg_base + kATmemO + (n & 1) * 32, r);
+                    tmem_ld_wait();
 #pragma unroll
-                                for (int j = 0; j < 32; ++j) m = fmaxf(m, __uint_as_float(v[j]));
-                            } else {
+                    for (int d = 0; d < D; ++d) o[d] = fmaf(o[d], alpha, __uint_as_float(r[d]));
+                    return true;
+                };
+                for (int c = 0; c < nc; ++c, ++cnt) {
+                    const uint32_t sb = cnt & 1;
+                    if (!wait_all(&bar.s_full[wg * 2 + sb], (cnt >> 1) & 1, 31)) return;
+                    tc_fence_after();
+                    uint32_t v0[32], v1[32];
+                    tmem_ld_32x32(wg_base + sb * kAKC, v0);
+                    tmem_ld_32x32(wg_base + sb * kAKC + 32, v1);
+                    tmem_ld_wait();
+                    const bool tail = (c == nc - 1) && tail_valid < kAKC;
+                    float mx = -INFINITY;
+                    if (!tail) {
 #pragma unroll
-                                for (int j = 0; j < 32; ++j)
-                                    if (key0 + half * 32 + j < p.Nk) m = fmaxf(m, __uint_as_float(v[j]));
-                            }
-                        }
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&bar.s_empty[sb]);
-                        ++s_it;
-                    }
-                    // ---- pass 2: P = exp2((S - m) * scale*log2e), row sums, P -> smem (K-major, 128-byte swizzle)
-                    const float mk = m * k2;
-                    float l = 0.f;
-                    for (int c = 0; c < nc; ++c) {
-                        const uint32_t sb = s_it & 1;
-                        if (!wait_all(&bar.s_full[sb], (s_it >> 1) & 1, 32)) return;
-                        tc_fence_after();
-                        uint32_t v0[32], v1[32];
-                        tmem_ld_32x32(lane_base + sb * kAKC, v0);
-                        tmem_ld_32x32(lane_base + sb * kAKC + 32, v1);
-                        tmem_ld_wait();
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&bar.s_empty[sb]);
-                        ++s_it;
-                        const int64_t key0 = (int64_t)c * kAKC;
-                        float pr[64];
+                        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, fmaxf(__uint_as_float(v0[j]), __uint_as_float(v1[j])));
+                    } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
-                            pr[j] = ex2_approx(fmaf(__uint_as_float(v0[j]), k2, -mk));
-                            pr[32 + j] = ex2_approx(fmaf(__uint_as_float(v1[j]), k2, -mk));
+                            if (j < tail_valid) mx = fmaxf(mx, __uint_as_float(v0[j]));
+                            if (32 + j < tail_valid) mx = fmaxf(mx, __uint_as_float(v1[j]));
                         }
-                        if (key0 + kAKC > p.Nk) {
-#pragma unroll
-                            for (int j = 0; j < 64; ++j)
-                                if (key0 + j >= p.Nk) pr[j] = 0.f;
-                        }
-#pragma unroll
-                        for (int j = 0; j < 64; ++j) l += pr[j];
-                        const uint32_t pb = p_it & 1;
-                        if (!wait_all(&bar.p_empty[pb], ((p_it >> 1) & 1) ^ 1, 33)) return;
-                        uint8_t* pbuf = base + kAPOff + pb * kAPBytes + row * 128;
-#pragma unroll
-                        for (int ch = 0; ch < 16; ++ch) {
-                            const float4 o = make_float4(pr[4 * ch], pr[4 * ch + 1], pr[4 * ch + 2], pr[4 * ch + 3]);
-                            *reinterpret_cast<float4*>(pbuf + (ch >> 3) * (kAQT * 128) + (((ch & 7) ^ (row & 7)) << 4)) = o;
-                        }
-                        fence_proxy_async();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&bar.p_full[pb]);
-                        ++p_it;
                     }
-                    // ---- epilogue of this head: O / l
-                    const uint32_t ob = o_it & 1;
-                    if (!wait_all(&bar.o_full[ob], (o_it >> 1) & 1, 34)) return;
-                    tc_fence_after();
-                    uint32_t o[D];
-                    if constexpr (D == 16) tmem_ld_32x16(lane_base + kATmemO + ob * 32 + hb * D, o);
-                    else tmem_ld_32x32(lane_base + kATmemO + ob * 32, o);
-                    tmem_ld_wait();
+                    const float m_new = fmaxf(m, mx);
+                    const float mk = m_new * k2;
+                    const float alpha = ex2_approx((m - m_new) * k2);      // m = -inf on the first chunk -> 0
+                    float ls = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        // P is truncated to tf32 here (what the MMA would do anyway) so that the row sum l matches
+                        // the values that enter P.V exactly
+                        uint32_t a = __float_as_uint(ex2_approx(fmaf(__uint_as_float(v0[j]), k2, -mk))) & 0xffffe000u;
+                        uint32_t bq = __float_as_uint(ex2_approx(fmaf(__uint_as_float(v1[j]), k2, -mk))) & 0xffffe000u;
+                        if (tail) {
+                            if (j >= tail_valid) a = 0u;
+                            if (32 + j >= tail_valid) bq = 0u;
+                        }
+                        v0[j] = a;
+                        v1[j] = bq;
+                        ls += __uint_as_float(a) + __uint_as_float(bq);
+                    }
+                    l = fmaf(l, alpha, ls);
+                    m = m_new;
+                    tmem_st_32x32(wg_base + sb * kAKC, v0);
+                    tmem_st_32x32(wg_base + sb * kAKC + 32, v1);
+                    tmem_st_wait();
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&bar.o_empty[ob]);
-                    ++o_it;
-                    if (qrow < p.Nq) {
-                        const float inv = 1.f / l;
-                        const int h = box * HB + hb;
-                        float* op = p.out + ((int64_t)b * p.Nq + qrow) * p.E + h * D;
+                    if (lane == 0) mbar_arrive(&bar.p_ready[wg * 2 + sb]);
+                    if (c > 0 && !fold(cnt - 1, alpha_prev)) return;
+                    alpha_prev = alpha;
+                }
+                if (!fold(cnt - 1, alpha_prev)) return;
+                tc_fence_before();
+                if (qrow < p.Nq) {
+                    const float inv = 1.f / l;
+                    const int h = box * HB + hb;
+                    float* op = p.out + ((int64_t)b * p.Nq + qrow) * p.E + h * D;
 #pragma unroll
-                        for (int d4 = 0; d4 < D / 4; ++d4) {
-                            float4 r;
-                            r.x = __uint_as_float(o[4 * d4]) * inv;
-                            r.y = __uint_as_float(o[4 * d4 + 1]) * inv;
-                            r.z = __uint_as_float(o[4 * d4 + 2]) * inv;
-                            r.w = __uint_as_float(o[4 * d4 + 3]) * inv;
-                            reinterpret_cast<float4*>(op)[d4] = r;
-                        }
-                        p.lse[((int64_t)b * p.H + h) * p.Nq + qrow] = m * p.scale + logf(l);
-                    }
+                    for (int d4 = 0; d4 < D / 4; ++d4)
+                        reinterpret_cast<float4*>(op)[d4] =
+                            make_float4(o[4 * d4] * inv, o[4 * d4 + 1] * inv, o[4 * d4 + 2] * inv, o[4 * d4 + 3] * inv);
+                    p.lse[((int64_t)b * p.H + h) * p.Nq + qrow] = m * p.scale + logf(l);
                 }
             }
         };
-        role();
+        if (U > 0) role();
     }
     tc_fence_before();
     __syncthreads();
