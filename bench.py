@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="attncnp_c2", choices=list(WORKLOADS))
-    ap.add_argument("--mode", default=os.environ.get("NPFK_MODE", "fp32"), choices=["fp32", "fast"])
+    ap.add_argument("--mode", default=os.environ.get("NPFK_MODE", "fast"), choices=["fp32", "fast"])
     ap.add_argument("--tasks-per-gpu", type=int, default=0, help="override the per-GPU batch (debugging only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline leg")
@@ -295,7 +295,7 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32" if args.mode == "fp32" else "f16 operands (11-bit mantissa, tf32-equivalent), f32 accumulate",
+        "dtype": "f32" if args.mode == "fp32" else "tf32 operands (tcgen05 kind::tf32), f32 accumulate, f32 storage",
         "data": "synthetic",
         "config": {"workload": WORKLOAD_TEXT[args.workload], "tasks_per_gpu": B, "global_batch": B * world,
                    "n_context": Nc, "n_target": Nt, "n_z": nz, "mode": args.mode,

@@ -22,3 +22,18 @@ for _ in range(2):
     y = Kn.mlp_chain(x, [(w1, b1), (w2, b1)])
     y.sum().backward()
 torch.cuda.synchronize()
+# SetConv induced -> target (C3 shape per task: 192 grid points, 4096 targets, 128 channels) and the Gaussian NLL
+Bs = 32
+grid = torch.linspace(-1.5, 1.5, 192, device="cuda")
+xt = torch.linspace(-1, 1, Nq, device="cuda")
+vals = torch.randn(Bs, 192, 128, device="cuda", requires_grad=True)
+theta = torch.tensor([-4.4], device="cuda", requires_grad=True)
+for _ in range(2):
+    o = Kn.setconv_rbf(grid, xt, vals, theta)
+    o.backward(torch.randn_like(o))
+suff = torch.randn(1, 256, Nq, 2, device="cuda", requires_grad=True)
+yt = torch.randn(256, Nq, 1, device="cuda")
+for _ in range(2):
+    lp = Kn.gauss_sum_log_prob(suff, yt)
+    lp.sum().backward()
+torch.cuda.synchronize()
