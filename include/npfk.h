@@ -128,6 +128,20 @@ int npfk_setconv_bwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq,
                      const float* theta, const float* out, const float* dout, int64_t ldo, float* dv,
                      float* dtheta, int B, int64_t Nk, int64_t Nq, int C, float p, int unshared, void* stream);
 
+/* SetConv with the resizer Linear hoisted onto the keys (grid -> many targets; setcnn.py:254-268):
+ *   out[b,q,:] = sum_k w_qk v[b,k,:] + density_q * wd + bias      v:[B,Nk,C] = values already multiplied by
+ * resizer.weight[:, :C_in]^T, wd:[C] = resizer.weight[:, C_in], bias:[C] or NULL.  out:[B,Nq,C] (row pitch C).
+ * stats:[B,Nq,2] = (density, softmax normaliser) saved for the backward pass.  Same RBF conventions as above.
+ * Keys whose weight is below 2^-40 of the row maximum (UnsharedExpRBF: below 1e-20) are skipped. */
+int npfk_setconv_interp_fwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq, const float* v,
+                            const float* theta, const float* wd, const float* bias, float* out, float* stats, int B,
+                            int64_t Nk, int64_t Nq, int C, float p, int unshared, void* stream);
+/* dv:[B,Nk,C] "+=" ; dwd:[C] "+=" ; dbias:[C] "+=" or NULL ; dtheta:[1 or 2] "+=". */
+int npfk_setconv_interp_bwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq, const float* v,
+                            const float* theta, const float* wd, const float* stats, const float* dout, float* dv,
+                            float* dwd, float* dbias, float* dtheta, int B, int64_t Nk, int64_t Nq, int C, float p,
+                            int unshared, void* stream);
+
 /* ---- 1-D depth-separable residual conv blocks, channel-last [B,L,C] ------------------------------
  * Replaces BatchNorm1d -> ReLU -> Conv1d(groups=C) of ResConvBlock.forward (npf/architectures/cnn.py:
  * 204-215, npf/utils/helpers.py:395-398) without the NLC<->NCL permutes (cnn.py:363-375).

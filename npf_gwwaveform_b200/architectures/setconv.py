@@ -63,5 +63,13 @@ class SetConv(nn.Module):
 
     def forward(self, keys, queries, values):
         rbf = self.radial_basis_func
+        n_in = values.shape[-1]
+        if queries.shape[-2] > keys.shape[-2] and self.resizer.in_features == n_in + 1:
+            # many queries per key (grid -> targets): the resizer is linear, so apply it to the keys' values and
+            # interpolate the result; out = sum_k w_qk (W_T v_k) + density_q * w_d + b is written once per query
+            w = self.resizer.weight
+            v = K.linear(values, w[:, :n_in])
+            return K.setconv_interp(keys, queries, v, rbf.length_scale_param, w[:, n_in], self.resizer.bias,
+                                    float(rbf.p), rbf.n_scales == 2)
         t = K.setconv_rbf(keys, queries, values, rbf.length_scale_param, float(rbf.p), rbf.n_scales == 2)
         return K.linear(t, self.resizer.weight, self.resizer.bias)

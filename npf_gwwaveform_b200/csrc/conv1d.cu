@@ -159,6 +159,73 @@ dwconv_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, con
     }
 }
 
+// Register-window variant for the common kernel sizes: a thread owns (channel, LC consecutive positions), loads the
+// LC + KS - 1 window of dy and of the activated input once (all loads independent -> deep memory parallelism) and
+// does the 2 * LC * KS FMAs from registers.  8x more CTAs than the chunk-of-64 kernel above and 4 instead of 38
+// loads per position; the generic kernel stays for other kernel sizes.
+template <int KS, int LC>
+__global__ void __launch_bounds__(128)
+dwconv_bwd_win_kernel(const float* __restrict__ dy, const float* __restrict__ x, const NormArgs nrm,
+                      const float* __restrict__ w, float* __restrict__ dh, float* __restrict__ dw,
+                      float* __restrict__ dbias, float* __restrict__ sums, int L, int C, int relu) {
+    constexpr int PAD = KS / 2, WN = LC + KS - 1;
+    const int c = blockIdx.x * 128 + threadIdx.x;
+    if (c >= C) return;
+    const int b = blockIdx.z;
+    const int l0 = blockIdx.y * LC;
+    float mean = 0.f, a = 1.f, beta = 0.f, invstd = 1.f;
+    if (nrm.mean) {
+        mean = __ldg(nrm.mean + c);
+        invstd = rsqrtf(__ldg(nrm.var + c) + nrm.eps);
+        a = __ldg(nrm.gamma + c) * invstd;
+        beta = __ldg(nrm.beta + c);
+    }
+    const float* xb = x + (int64_t)b * L * C + c;
+    const float* dyb = dy + (int64_t)b * L * C + c;
+    float* dhb = dh + (int64_t)b * L * C + c;
+    float dyw[WN], hw[WN], xc[LC];
+#pragma unroll
+    for (int i = 0; i < WN; ++i) {
+        const int li = l0 - PAD + i;
+        const bool ok = li >= 0 && li < L;
+        dyw[i] = ok ? __ldg(dyb + (int64_t)li * C) : 0.f;
+        const float xv = ok ? __ldg(xb + (int64_t)li * C) : 0.f;
+        hw[i] = ok ? pre_act(xv, mean, a, beta, relu) : 0.f;
+        if (i >= PAD && i < PAD + LC) xc[i - PAD] = xv;
+    }
+    float wr[KS], dwacc[KS];
+#pragma unroll
+    for (int j = 0; j < KS; ++j) {
+        wr[j] = __ldg(w + c * KS + j);
+        dwacc[j] = 0.f;
+    }
+    float sb = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int l = 0; l < LC; ++l) {
+        if (l0 + l < L) {
+            float g = 0.f;
+#pragma unroll
+            for (int j = 0; j < KS; ++j) g = fmaf(wr[j], dyw[l - j + 2 * PAD], g);
+            const float hpre = (xc[l] - mean) * a + beta;
+            if (relu && !(hpre > 0.f)) g = 0.f;
+            dhb[(int64_t)(l0 + l) * C] = g;
+            s1 += g;
+            s2 = fmaf(g, (xc[l] - mean) * invstd, s2);
+            const float dyv = dyw[l + PAD];
+            sb += dyv;
+#pragma unroll
+            for (int j = 0; j < KS; ++j) dwacc[j] = fmaf(dyv, hw[l + j], dwacc[j]);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < KS; ++j) atomicAdd(dw + c * KS + j, dwacc[j]);
+    if (dbias) atomicAdd(dbias + c, sb);
+    if (sums) {
+        atomicAdd(sums + c, s1);
+        atomicAdd(sums + C + c, s2);
+    }
+}
+
 __global__ void bn_bwd_kernel(const float* dh, const float* __restrict__ x, const float* __restrict__ mean,
                               const float* __restrict__ var, const float* __restrict__ gamma, float eps,
                               const float* __restrict__ sums, float* dx, float* __restrict__ dgamma,
@@ -324,6 +391,22 @@ int npfk_dwconv_bwd(const float* dy, const float* x, const float* mean, const fl
     NPFK_REQUIRE(ks > 0 && ks % 2 == 1 && ks <= kDwMaxKs, "dwconv_bwd: kernel size %d must be odd and <= %d", ks, kDwMaxKs);
     NPFK_REQUIRE(!mean || (var && gamma && beta), "dwconv_bwd: incomplete normalisation arguments");
     NormArgs n{mean, var, gamma, beta, eps};
+    constexpr int kWinLC = 16;
+    dim3 wgrid((C + 127) / 128, (L + kWinLC - 1) / kWinLC, B);
+#define NPFK_DW_WIN(KS_)                                                                                              \
+    case KS_:                                                                                                         \
+        NPFK_LAUNCH((dwconv_bwd_win_kernel<KS_, kWinLC>), wgrid, 128, 0, as_stream(stream), dy, x, n, w, dh, dw,      \
+                    dbias, sums, L, C, relu);                                                                         \
+        return check_launch("dwconv_bwd_win");
+    switch (ks) {
+        NPFK_DW_WIN(3)
+        NPFK_DW_WIN(5)
+        NPFK_DW_WIN(7)
+        NPFK_DW_WIN(11)
+        NPFK_DW_WIN(19)
+        default: break;
+    }
+#undef NPFK_DW_WIN
     dim3 grid((C + 127) / 128, (L + kDwLChunk - 1) / kDwLChunk, B);
     NPFK_LAUNCH(dwconv_bwd_kernel, grid, 128, 0, as_stream(stream), dy, x, n, w, dh, dw, dbias, sums, L, C, ks, relu);
     return check_launch("dwconv_bwd");

@@ -1,0 +1,443 @@
+// SetConv grid -> target interpolation with the resizer hoisted onto the keys (ConvCNP induced -> target).
+//
+// Reference: SetConv.forward (npf/architectures/setcnn.py:254-268) computes
+//     out_q = W_T (sum_k w_qk v_k) + w_d * density_q + b          with  resizer.weight = [W_T | w_d]
+// on every one of the B*Nq target rows (a [B*Nq, C+1] x [C+1, O] GEMM after a [B,Nq,Nk,C] broadcast product).
+// The resizer is linear, so it is applied once per KEY instead (v'_k = W_T v_k, a [B*Nk, C] GEMM with Nk = 192
+// grid points) and this kernel produces the final rows directly:
+//     out_q = sum_k w_qk v'_k + density_q * w_d + b
+// HBM traffic per target row: one 4*O-byte write forward, one 4*O-byte read backward (540 B
+// per target is the algorithmic figure of the unhoisted form).
+//
+// The RBF weights decay like exp(-(d/sigma)^p): a key contributes less than 2^-40 of the row's largest weight
+// once (d/sigma)^p exceeds the nearest key's by 28, which is below fp32 resolution of the sum.  Keys are visited
+// in chunks of 32; a chunk is skipped when its [min,max] position interval is that far from every query of the
+// CTA, and inside a visited chunk only keys with a non-negligible weight for some query reach the value phase.
+// No assumption is made on key order: unsorted keys only make the skip test succeed less often.
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace npfk {
+
+constexpr int kIThreads = 128;
+constexpr int kIQ = 64;     // queries per CTA
+constexpr int kIK = 32;     // keys per chunk
+constexpr int kIC = 128;    // channels per pass (one per thread)
+constexpr float kCutShared = -28.f;     // exp(-28) = 6.9e-13 relative to the row maximum
+constexpr float kCutUnshared = -46.f;   // exp(-46) = 1.1e-20 absolute (weights are divided by density + 1e-8)
+
+struct InterpArgs {
+    const float* xk; int64_t sxk;
+    const float* xq; int64_t sxq;
+    const float* v;        // [B,Nk,C] values with the resizer already applied
+    const float* theta;    // [1] or [2]
+    const float* wd;       // [C] density column of the resizer weight
+    const float* bias;     // [C] or null
+    int64_t Nk, Nq; int C; float p; int unshared;
+};
+
+__device__ __forceinline__ float interp_inp_d(float d, float sigma, float p) {
+    // reference op order: dist / sigma, then pow(p), then negate (setcnn.py:131-132)
+    const float t = d / sigma;
+    return (p == 2.f) ? -(t * t) : -powf(t, p);
+}
+
+// distance to the nearest key of the batch element, per query (identical in both key-half threads afterwards)
+__device__ __forceinline__ float nearest_key_dist(const InterpArgs& a, int b, float xq, int half, int ql, float* sK,
+                                                  float* sRed) {
+    float dmin = CUDART_INF_F;
+    for (int64_t k0 = 0; k0 < a.Nk; k0 += kIThreads) {
+        const int n = (int)min((int64_t)kIThreads, a.Nk - k0);
+        __syncthreads();
+        if (threadIdx.x < n) sK[threadIdx.x] = __ldg(a.xk + (int64_t)b * a.sxk + k0 + threadIdx.x);
+        __syncthreads();
+        for (int j = half; j < n; j += 2) dmin = fminf(dmin, fabsf(sK[j] - xq));
+    }
+    __syncthreads();
+    sRed[threadIdx.x] = dmin;
+    __syncthreads();
+    return fminf(sRed[ql], sRed[ql + kIQ]);
+}
+
+// loads key chunk k0 into sXk, publishes its position interval in sBnd and clears the per-key flags;
+// returns (CTA-uniform) whether any valid query of the CTA can receive a non-negligible weight from the chunk
+__device__ __forceinline__ bool chunk_begin(const InterpArgs& a, int b, int64_t k0, int nk, float xq, bool qv, float m,
+                                            float sigma, float sigma_d, float* sXk, float* sBnd, int* sAct) {
+    __syncthreads();
+    if (threadIdx.x < kIK) {
+        const bool ok = threadIdx.x < nk;
+        const float x = ok ? __ldg(a.xk + (int64_t)b * a.sxk + k0 + threadIdx.x) : 0.f;
+        sXk[threadIdx.x] = x;
+        sAct[threadIdx.x] = 0;
+        float lo = ok ? x : CUDART_INF_F, hi = ok ? x : -CUDART_INF_F;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+            hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        }
+        if (threadIdx.x == 0) {
+            sBnd[0] = lo;
+            sBnd[1] = hi;
+        }
+    }
+    __syncthreads();
+    const float dq = fmaxf(0.f, fmaxf(sBnd[0] - xq, xq - sBnd[1]));
+    bool hit;
+    if (a.unshared)
+        hit = fmaxf(interp_inp_d(dq, sigma, a.p), interp_inp_d(dq, sigma_d, a.p)) > kCutUnshared;
+    else
+        hit = interp_inp_d(dq, sigma, a.p) - m > kCutShared;
+    return __syncthreads_or(qv && hit) != 0;
+}
+
+__global__ void __launch_bounds__(kIThreads, 3)
+setconv_interp_fwd_kernel(const InterpArgs a, float* __restrict__ out, float* __restrict__ stats) {
+    __shared__ __align__(16) float sW[kIK][kIQ];   // un-normalised weights of the current key chunk
+    __shared__ float sXk[kIK];
+    __shared__ int sAct[kIK];
+    __shared__ float sBnd[2];
+    __shared__ float sK[kIThreads];
+    __shared__ float sRed[kIThreads];
+    __shared__ float sInvL[kIQ];
+    __shared__ float sDens[kIQ];
+    const int b = blockIdx.y;
+    const int ql = threadIdx.x % kIQ, half = threadIdx.x / kIQ;
+    const int64_t q0 = (int64_t)blockIdx.x * kIQ;
+    const int nq = (int)min((int64_t)kIQ, a.Nq - q0);
+    const bool qv = ql < nq;
+    const float xq = qv ? __ldg(a.xq + (int64_t)b * a.sxq + q0 + ql) : 0.f;
+    const float sigma = 1e-5f + softplus_f(__ldg(a.theta));
+    const float sigma_d = a.unshared ? 1e-5f + softplus_f(__ldg(a.theta + 1)) : sigma;
+
+    float m = 0.f;
+    if (!a.unshared) m = interp_inp_d(nearest_key_dist(a, b, xq, half, ql, sK, sRed), sigma, a.p);
+
+    for (int c0 = 0; c0 < a.C; c0 += kIC) {
+        const int c = c0 + threadIdx.x;
+        float acc[kIQ];
+#pragma unroll
+        for (int i = 0; i < kIQ; ++i) acc[i] = 0.f;
+        float l = 0.f;   // sum of un-normalised weights (shared) or of the density terms (unshared), per (q, half)
+        for (int64_t k0 = 0; k0 < a.Nk; k0 += kIK) {
+            const int nk = (int)min((int64_t)kIK, a.Nk - k0);
+            if (!chunk_begin(a, b, k0, nk, xq, qv, m, sigma, sigma_d, sXk, sBnd, sAct)) continue;
+            for (int j = half; j < kIK; j += 2) {
+                float e = 0.f;
+                if (j < nk && qv) {
+                    const float d = fabsf(sXk[j] - xq);
+                    if (a.unshared) {
+                        const float i0 = interp_inp_d(d, sigma, a.p), i1 = interp_inp_d(d, sigma_d, a.p);
+                        e = expf(i0);
+                        l += expf(i1);
+                        if (fmaxf(i0, i1) > kCutUnshared) sAct[j] = 1;
+                    } else {
+                        const float i0 = interp_inp_d(d, sigma, a.p) - m;
+                        e = expf(i0);
+                        l += e;
+                        if (i0 > kCutShared) sAct[j] = 1;
+                    }
+                }
+                sW[j][ql] = e;
+            }
+            __syncthreads();
+            if (c < a.C) {
+                for (int j = 0; j < nk; ++j) {
+                    if (!sAct[j]) continue;
+                    const float vv = __ldg(a.v + ((int64_t)b * a.Nk + k0 + j) * a.C + c);
+#pragma unroll
+                    for (int i = 0; i < kIQ; i += 4) {
+                        const float4 w4 = *reinterpret_cast<const float4*>(&sW[j][i]);
+                        acc[i] = fmaf(w4.x, vv, acc[i]);
+                        acc[i + 1] = fmaf(w4.y, vv, acc[i + 1]);
+                        acc[i + 2] = fmaf(w4.z, vv, acc[i + 2]);
+                        acc[i + 3] = fmaf(w4.w, vv, acc[i + 3]);
+                    }
+                }
+            }
+        }
+        // merge the two key halves: normaliser and density per query
+        __syncthreads();
+        sRed[threadIdx.x] = l;
+        __syncthreads();
+        if (threadIdx.x < kIQ) {
+            const float lt = sRed[ql] + sRed[ql + kIQ];
+            float density, inv;
+            if (a.unshared) {
+                density = lt;
+                inv = 1.f / (lt + 1e-8f);
+            } else {
+                density = lt * expf(m);
+                inv = 1.f / lt;
+            }
+            sInvL[ql] = inv;
+            sDens[ql] = density;
+            if (c0 == 0 && qv) {
+                stats[((int64_t)b * a.Nq + q0 + ql) * 2] = density;
+                stats[((int64_t)b * a.Nq + q0 + ql) * 2 + 1] = lt;
+            }
+        }
+        __syncthreads();
+        if (c < a.C) {
+            const float wdc = __ldg(a.wd + c);
+            const float bc = a.bias ? __ldg(a.bias + c) : 0.f;
+            float* op = out + ((int64_t)b * a.Nq + q0) * a.C + c;
+#pragma unroll
+            for (int i = 0; i < kIQ; ++i)
+                if (i < nq) op[(int64_t)i * a.C] = fmaf(acc[i], sInvL[i], fmaf(sDens[i], wdc, bc));
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ backward
+struct InterpBwdSmem {
+    float dT[kIC][kIQ + 1];   // dout tile, channel-major (conflict-free for row and column readers)
+    float V[kIK][kIC];        // value rows of the active keys of the chunk (compacted)
+    float W[kIK][kIQ];        // normalised weights
+    float Xk[kIK];
+    float K[kIThreads];
+    float Red[kIThreads];
+    float Red4[4][kIThreads];
+    int Act[kIK];
+    int ActIdx[kIK];
+    int nAct;
+    float Bnd[2];
+};
+
+// dv:[B,Nk,C] "+=", dwd:[C] "+=", dbias:[C] "+=" (may be null), dtheta:[1 or 2] "+="
+__global__ void __launch_bounds__(kIThreads, 3)
+setconv_interp_bwd_kernel(const InterpArgs a, const float* __restrict__ stats, const float* __restrict__ dout,
+                          float* __restrict__ dv, float* __restrict__ dwd, float* __restrict__ dbias,
+                          float* __restrict__ dtheta) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    InterpBwdSmem& s = *reinterpret_cast<InterpBwdSmem*>(smem_raw);
+    const int b = blockIdx.y;
+    const int ql = threadIdx.x % kIQ, half = threadIdx.x / kIQ;
+    const int64_t q0 = (int64_t)blockIdx.x * kIQ;
+    const int nq = (int)min((int64_t)kIQ, a.Nq - q0);
+    const bool qv = ql < nq;
+    const float xq = qv ? __ldg(a.xq + (int64_t)b * a.sxq + q0 + ql) : 0.f;
+    const float th0 = __ldg(a.theta);
+    const float sigma = 1e-5f + softplus_f(th0);
+    const float th1 = a.unshared ? __ldg(a.theta + 1) : th0;
+    const float sigma_d = a.unshared ? 1e-5f + softplus_f(th1) : sigma;
+    const bool single = a.C <= kIC;
+
+    float m = 0.f;
+    if (!a.unshared) m = interp_inp_d(nearest_key_dist(a, b, xq, half, ql, s.K, s.Red), sigma, a.p);
+    const float dens = qv ? __ldg(stats + ((int64_t)b * a.Nq + q0 + ql) * 2) : 0.f;
+    const float lsum = qv ? __ldg(stats + ((int64_t)b * a.Nq + q0 + ql) * 2 + 1) : 1.f;
+    const float inv_l = a.unshared ? 1.f / (lsum + 1e-8f) : 1.f / lsum;
+    const float emax = a.unshared ? 1.f : expf(m);
+
+    // dout tile of channel pass c0 -> s.dT (transposed); rows beyond nq / channels beyond C are zero
+    auto stage_dT = [&](int c0) {
+        const int ncc = min(kIC, a.C - c0);
+        for (int e = threadIdx.x; e < kIQ * kIC; e += kIThreads) {
+            const int qq = e / kIC, cc = e % kIC;
+            s.dT[cc][qq] = (qq < nq && cc < ncc) ? __ldg(dout + ((int64_t)b * a.Nq + q0 + qq) * a.C + c0 + cc) : 0.f;
+        }
+    };
+    float r[kIQ];   // this thread's channel row of the dout tile (kept across the key loop when C <= 128)
+
+    // ---- prologue over channel passes: d bias, d wd, and d density_q = dout_q . wd
+    float ddens = 0.f;
+    for (int c0 = 0; c0 < a.C; c0 += kIC) {
+        const int ncc = min(kIC, a.C - c0);
+        __syncthreads();
+        stage_dT(c0);
+        s.Red[threadIdx.x] = dens;     // Red[0..63] = density per query (both halves write the same value)
+        __syncthreads();
+        if ((int)threadIdx.x < ncc) {
+            float sb = 0.f, sd = 0.f;
+#pragma unroll
+            for (int i = 0; i < kIQ; ++i) {
+                r[i] = s.dT[threadIdx.x][i];
+                sb += r[i];
+                sd = fmaf(r[i], s.Red[i], sd);
+            }
+            if (dbias) atomicAdd(dbias + c0 + threadIdx.x, sb);
+            atomicAdd(dwd + c0 + threadIdx.x, sd);
+        }
+        for (int cc = half; cc < ncc; cc += 2) ddens = fmaf(s.dT[cc][ql], __ldg(a.wd + c0 + cc), ddens);
+    }
+    __syncthreads();
+    s.Red[threadIdx.x] = ddens;
+    __syncthreads();
+    ddens = s.Red[ql] + s.Red[ql + kIQ];
+
+    // per-(query, key-half) partial sums over the active keys
+    float sA = 0.f, sB = 0.f, sDot = 0.f, sD = 0.f;
+    for (int64_t k0 = 0; k0 < a.Nk; k0 += kIK) {
+        const int nk = (int)min((int64_t)kIK, a.Nk - k0);
+        if (!chunk_begin(a, b, k0, nk, xq, qv, m, sigma, sigma_d, s.Xk, s.Bnd, s.Act)) continue;
+        for (int j = half; j < kIK; j += 2) {
+            float w = 0.f;
+            if (j < nk && qv) {
+                const float d = fabsf(s.Xk[j] - xq);
+                if (a.unshared) {
+                    const float i0 = interp_inp_d(d, sigma, a.p), i1 = interp_inp_d(d, sigma_d, a.p);
+                    w = expf(i0) * inv_l;
+                    if (fmaxf(i0, i1) > kCutUnshared) s.Act[j] = 1;
+                } else {
+                    const float i0 = interp_inp_d(d, sigma, a.p) - m;
+                    w = expf(i0) * inv_l;
+                    if (i0 > kCutShared) s.Act[j] = 1;
+                }
+            }
+            s.W[j][ql] = w;
+        }
+        __syncthreads();
+        if (threadIdx.x < kIK) {   // compact the active keys of the chunk
+            const bool act = s.Act[threadIdx.x] != 0;
+            const unsigned mask = __ballot_sync(0xffffffffu, act);
+            if (act) s.ActIdx[__popc(mask & ((1u << threadIdx.x) - 1u))] = threadIdx.x;
+            if (threadIdx.x == 0) s.nAct = __popc(mask);
+        }
+        __syncthreads();
+        const int nAct = s.nAct;
+        float dp[kIK / 2];   // dout_q . v_k for this thread's active keys a = half + 2*i
+#pragma unroll
+        for (int i = 0; i < kIK / 2; ++i) dp[i] = 0.f;
+
+        for (int c0 = 0; c0 < a.C; c0 += kIC) {
+            const int ncc = min(kIC, a.C - c0);
+            if (!single) {
+                __syncthreads();
+                stage_dT(c0);
+            }
+            for (int e = threadIdx.x; e < nAct * kIC; e += kIThreads) {
+                const int aa = e / kIC, cc = e % kIC;
+                s.V[aa][cc] = cc < ncc ? __ldg(a.v + ((int64_t)b * a.Nk + k0 + s.ActIdx[aa]) * a.C + c0 + cc) : 0.f;
+            }
+            __syncthreads();
+            if (!single && (int)threadIdx.x < ncc) {
+#pragma unroll
+                for (int i = 0; i < kIQ; ++i) r[i] = s.dT[threadIdx.x][i];
+            }
+            // dp[q][k] += sum_c dT[q][c] v[k][c]      (thread = (q, key-half))
+            for (int cc = 0; cc < ncc; ++cc) {
+                const float t = s.dT[cc][ql];
+#pragma unroll
+                for (int i = 0; i < kIK / 2; ++i)
+                    if (half + 2 * i < nAct) dp[i] = fmaf(t, s.V[half + 2 * i][cc], dp[i]);
+            }
+            // dv[k][c] += sum_q w[k][q] dT[q][c]        (thread = channel, dout row in registers)
+            if ((int)threadIdx.x < ncc) {
+                for (int aa = 0; aa < nAct; ++aa) {
+                    const int j = s.ActIdx[aa];
+                    float accv = 0.f;
+#pragma unroll
+                    for (int i = 0; i < kIQ; i += 4) {
+                        const float4 w4 = *reinterpret_cast<const float4*>(&s.W[j][i]);
+                        accv = fmaf(w4.x, r[i], accv);
+                        accv = fmaf(w4.y, r[i + 1], accv);
+                        accv = fmaf(w4.z, r[i + 2], accv);
+                        accv = fmaf(w4.w, r[i + 3], accv);
+                    }
+                    atomicAdd(dv + ((int64_t)b * a.Nk + k0 + j) * a.C + c0 + threadIdx.x, accv);
+                }
+            }
+            if (!single) __syncthreads();
+        }
+        // length-scale terms of this thread's (query, active keys)
+        if (qv) {
+#pragma unroll
+            for (int i = 0; i < kIK / 2; ++i) {
+                if (half + 2 * i < nAct) {
+                    const int j = s.ActIdx[half + 2 * i];
+                    const float d = fabsf(s.Xk[j] - xq);
+                    const float inp = interp_inp_d(d, sigma, a.p);
+                    const float w = s.W[j][ql];
+                    sDot = fmaf(w, dp[i], sDot);
+                    if (a.unshared) {
+                        sA = fmaf(w * dp[i], inp, sA);
+                        const float i1 = interp_inp_d(d, sigma_d, a.p);
+                        sD = fmaf(expf(i1), i1, sD);
+                    } else {
+                        // softmax part: sum_k w_k (dp_k - dot)(inp_k - m) = sA - dot * sB, with the row maximum
+                        // subtracted so far queries (|m| ~ 1e4) do not cancel catastrophically
+                        sA = fmaf(w * dp[i], inp - m, sA);
+                        sB = fmaf(w, inp - m, sB);
+                        sD = fmaf(expf(inp - m) * emax, inp, sD);
+                    }
+                }
+            }
+        }
+    }
+    // merge the key halves per query, then reduce d sigma over the CTA
+    __syncthreads();
+    s.Red4[0][threadIdx.x] = sA;
+    s.Red4[1][threadIdx.x] = sB;
+    s.Red4[2][threadIdx.x] = sDot;
+    s.Red4[3][threadIdx.x] = sD;
+    __syncthreads();
+    float dsig0 = 0.f, dsig1 = 0.f;
+    if (threadIdx.x < kIQ && qv) {
+        const float A = s.Red4[0][ql] + s.Red4[0][ql + kIQ], Bq = s.Red4[1][ql] + s.Red4[1][ql + kIQ];
+        const float dot = s.Red4[2][ql] + s.Red4[2][ql + kIQ], D = s.Red4[3][ql] + s.Red4[3][ql + kIQ];
+        if (a.unshared) {
+            dsig0 = A * (-a.p / sigma);
+            dsig1 = (ddens - dot * inv_l) * D * (-a.p / sigma_d);
+        } else {
+            dsig0 = (A - dot * Bq + ddens * D) * (-a.p / sigma);
+        }
+    }
+    dsig0 = warp_sum(dsig0);
+    dsig1 = warp_sum(dsig1);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) {
+        s.Red[threadIdx.x >> 5] = dsig0;
+        s.Red[4 + (threadIdx.x >> 5)] = dsig1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        atomicAdd(dtheta, (s.Red[0] + s.Red[1] + s.Red[2] + s.Red[3]) * sigmoid_f(th0));
+        if (a.unshared) atomicAdd(dtheta + 1, (s.Red[4] + s.Red[5] + s.Red[6] + s.Red[7]) * sigmoid_f(th1));
+    }
+}
+
+}  // namespace npfk
+
+using namespace npfk;
+
+extern "C" {
+
+int npfk_setconv_interp_fwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq, const float* v,
+                            const float* theta, const float* wd, const float* bias, float* out, float* stats, int B,
+                            int64_t Nk, int64_t Nq, int C, float p, int unshared, void* stream) {
+    NPFK_REQUIRE(xk && xq && v && theta && wd && out && stats, "setconv_interp_fwd: null pointer");
+    NPFK_REQUIRE(B > 0 && B <= 65535 && Nk > 0 && Nq > 0 && C > 0, "setconv_interp_fwd: bad shape B=%d Nk=%lld Nq=%lld C=%d",
+                 B, (long long)Nk, (long long)Nq, C);
+    NPFK_REQUIRE(p > 0.f, "setconv_interp_fwd: p must be positive");
+    InterpArgs a{xk, sxk, xq, sxq, v, theta, wd, bias, Nk, Nq, C, p, unshared};
+    dim3 grid((unsigned)ceil_div64(Nq, kIQ), B);
+    NPFK_LAUNCH(setconv_interp_fwd_kernel, grid, kIThreads, 0, as_stream(stream), a, out, stats);
+    return check_launch("setconv_interp_fwd");
+}
+
+int npfk_setconv_interp_bwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq, const float* v,
+                            const float* theta, const float* wd, const float* stats, const float* dout, float* dv,
+                            float* dwd, float* dbias, float* dtheta, int B, int64_t Nk, int64_t Nq, int C, float p,
+                            int unshared, void* stream) {
+    NPFK_REQUIRE(xk && xq && v && theta && wd && stats && dout && dv && dwd && dtheta, "setconv_interp_bwd: null pointer");
+    NPFK_REQUIRE(B > 0 && B <= 65535 && Nk > 0 && Nq > 0 && C > 0, "setconv_interp_bwd: bad shape");
+    NPFK_REQUIRE(p > 0.f, "setconv_interp_bwd: p must be positive");
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(setconv_interp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)sizeof(InterpBwdSmem));
+        if (e != cudaSuccess) {
+            set_error("setconv_interp_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+            return NPFK_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    InterpArgs a{xk, sxk, xq, sxq, v, theta, wd, nullptr, Nk, Nq, C, p, unshared};
+    dim3 grid((unsigned)ceil_div64(Nq, kIQ), B);
+    NPFK_LAUNCH(setconv_interp_bwd_kernel, grid, kIThreads, sizeof(InterpBwdSmem), as_stream(stream), a, stats, dout, dv,
+                dwd, dbias, dtheta);
+    return check_launch("setconv_interp_bwd");
+}
+
+}  // extern "C"

@@ -467,6 +467,44 @@ def setconv_rbf(xk, xq, v, theta, p=2.0, unshared=False):
     return _SetConvRbfFn.apply(xk, xq, v, theta, p, unshared)
 
 
+class _SetConvInterpFn(Function):
+    @staticmethod
+    def forward(ctx, xk, xq, v, theta, wd, bias, p: float, unshared: bool):
+        # v:[B,Nk,C] (resizer already applied to the values)  wd:[C]  bias:[C]|None  -> [B,Nq,C]
+        require_cuda(xk, xq, v, theta, wd, bias)
+        v, theta, wd, bias = _c(v), _c(theta), _c(wd), _c(bias)
+        B, Nk, C = v.shape
+        xk, sxk = _positions(xk, B, Nk)
+        xq, sxq = _positions(xq, B, None)
+        Nq = xq.numel() if sxq == 0 else xq.numel() // B
+        out = torch.empty(B, Nq, C, device=v.device, dtype=torch.float32)
+        stats = torch.empty(B, Nq, 2, device=v.device, dtype=torch.float32)
+        LIB.call("npfk_setconv_interp_fwd", _p(xk), sxk, _p(xq), sxq, _p(v), _p(theta), _p(wd), _p(bias), _p(out),
+                 _p(stats), B, Nk, Nq, C, float(p), int(unshared), _st())
+        ctx.save_for_backward(xk, xq, v, theta, wd, stats)
+        ctx.cfg = (sxk, sxq, B, Nk, Nq, C, float(p), int(unshared), bias is not None)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xk, xq, v, theta, wd, stats = ctx.saved_tensors
+        sxk, sxq, B, Nk, Nq, C, p, unshared, has_bias = ctx.cfg
+        dout = _c(dout)
+        dv = torch.zeros_like(v)
+        dtheta = torch.zeros_like(theta)
+        dwd = torch.zeros_like(wd)
+        dbias = torch.zeros_like(wd) if has_bias else None
+        LIB.call("npfk_setconv_interp_bwd", _p(xk), sxk, _p(xq), sxq, _p(v), _p(theta), _p(wd), _p(stats), _p(dout),
+                 _p(dv), _p(dwd), _p(dbias), _p(dtheta), B, Nk, Nq, C, p, unshared, _st())
+        return None, None, dv, dtheta, dwd, dbias, None, None
+
+
+def setconv_interp(xk, xq, v, theta, wd, bias=None, p=2.0, unshared=False):
+    """sum_k w_qk v_k + density_q * wd + bias: SetConv with its resizer already applied to the values `v`
+    (grid -> targets direction, many more queries than keys); positions get no gradient."""
+    return _SetConvInterpFn.apply(xk, xq, v, theta, wd, bias, p, unshared)
+
+
 # ------------------------------------------------------------------------------------------ conv blocks
 class _NormActDwConvFn(Function):
     """y = dwconv(act(norm(x))) + bias + res on channel-last [B,L,C]; BatchNorm statistics handled inside."""

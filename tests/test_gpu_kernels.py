@@ -199,6 +199,49 @@ def test_setconv(B, Nk, Nq, C, unshared, shared_grid):
     check_grads(["dv", "dtheta", "dW"], [vd.grad, td.grad, Wd.grad], [vs.grad, ts.grad, Ws.grad])
 
 
+@pytest.mark.parametrize("B,Nk,Nq,C,O_,unshared,keys", [
+    (2, 48, 70, 32, 24, False, "grid"),       # induced grid -> targets
+    (1, 192, 4096, 128, 128, False, "grid"),  # C3 shape of one task: most key chunks are skipped
+    (2, 192, 130, 128, 128, False, "grid"),
+    (2, 70, 200, 16, 160, False, "random"),   # unsorted keys, two channel passes of the output
+    (2, 40, 90, 16, 24, True, "grid"),        # fork's UnsharedExpRBF
+    (1, 1, 3, 2, 8, False, "random"),
+    (2, 33, 65, 8, 16, False, "clustered"),   # queries far from every key (softmax max far below 0)
+])
+def test_setconv_interp_hoisted_resizer(B, Nk, Nq, C, O_, unshared, keys):
+    """SetConv.forward with the resizer applied to the keys' values first (npfk_setconv_interp_*), against the
+    oracle's unhoisted restatement of setcnn.py:254-268."""
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    g = torch.Generator().manual_seed(Nk * 5 + Nq)
+    if keys == "grid":
+        xk = torch.linspace(-1.5, 1.5, Nk).view(1, Nk, 1).expand(B, Nk, 1)
+    elif keys == "clustered":
+        xk = torch.rand(B, Nk, 1, generator=g) * 0.2 - 0.9
+    else:
+        xk = torch.rand(B, Nk, 1, generator=g) * 2 - 1
+    xq = torch.rand(B, Nq, 1, generator=g) * 2 - 1
+    v = torch.randn(B, Nk, C, generator=g)
+    sig = 3.0 / max(Nk, 8)
+    theta = torch.full((2 if unshared else 1,), math.log(math.expm1(sig)))
+    if unshared:
+        theta[1] += 0.3
+    W, bias = torch.randn(O_, C + 1, generator=g) / math.sqrt(C + 1), torch.randn(O_, generator=g)
+    dy = torch.randn(B, Nq, O_, generator=g)
+
+    ts, vs, Ws, bs = cpu(theta, True), cpu(v, True), cpu(W, True), cpu(bias, True)
+    ref = _setconv_ref(xk.double(), xq.double(), vs, ts, Ws, bs, unshared)
+    ref.backward(dy.double())
+
+    td, vd, Wd, bd = dev(theta, True), dev(v, True), dev(W, True), dev(bias, True)
+    vp = Kn.linear(vd, Wd[:, :C])
+    out = Kn.setconv_interp(xk.cuda(), xq.cuda(), vp, td, Wd[:, C], bd, 2.0, unshared)
+    out.backward(dy.cuda())
+    assert rel_err(out, ref) < TOL
+    check_grads(["dv", "dW", "db"], [vd.grad, Wd.grad, bd.grad], [vs.grad, Ws.grad, bs.grad])
+    check_grads(["dtheta"], [td.grad], [ts.grad], tol=2e-3)
+
+
 def test_setconv_far_queries_are_defined():
     """G3: softmax weights stay defined when every exp underflows; density -> 0 (setcnn.py:134-140)"""
     from npf_gwwaveform_b200 import kernels as Kn

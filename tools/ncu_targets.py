@@ -28,8 +28,10 @@ grid = torch.linspace(-1.5, 1.5, 192, device="cuda")
 xt = torch.linspace(-1, 1, Nq, device="cuda")
 vals = torch.randn(Bs, 192, 128, device="cuda", requires_grad=True)
 theta = torch.tensor([-4.4], device="cuda", requires_grad=True)
+wd = torch.randn(128, device="cuda", requires_grad=True)
+bs = torch.zeros(128, device="cuda", requires_grad=True)
 for _ in range(2):
-    o = Kn.setconv_rbf(grid, xt, vals, theta)
+    o = Kn.setconv_interp(grid, xt, vals, theta, wd, bs)
     o.backward(torch.randn_like(o))
 suff = torch.randn(1, 256, Nq, 2, device="cuda", requires_grad=True)
 yt = torch.randn(256, Nq, 1, device="cuda")
