@@ -57,6 +57,13 @@ int npfk_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw,
 /* dw[n,k] += sum_m g[m,n] x[m,k] ; db[n] += sum_m g[m,n]  (db may be NULL) */
 int npfk_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx, float* dw, int64_t lddw,
                        float* db, int64_t M, int N, int K, int mode, void* stream);
+/* dgrad + wgrad of one layer in one call: dx = (g . w) masked by (x > 0) when `masked`, dw += g^T . x,
+ * db += sum_m g.  In NPFK_MODE_FAST with N == K == 128 this is ONE tcgen05 kernel that reads g and x from
+ * HBM once (the ReLU mask is taken from x, the layer's saved input, which is also the wgrad operand);
+ * every other shape/mode runs npfk_linear_bwd_dw followed by npfk_linear_bwd_dx. */
+int npfk_linear_bwd_fused(const float* g, int64_t ldg, const float* x, int64_t ldx, const float* w, int64_t ldw,
+                          int masked, float* dx, int64_t lddx, float* dw, int64_t lddw, float* db, int64_t M, int N,
+                          int K, int mode, void* stream);
 /* dst[i] = round-to-nearest tf32(src[i]) (weights, before they meet tcgen05.mma.kind::tf32 which truncates) */
 int npfk_round_tf32(const float* src, float* dst, int64_t n, void* stream);
 /* != 0 when a tcgen05 kernel gave up on a bounded mbarrier wait since the last call (synchronises; tests only) */

@@ -245,6 +245,10 @@ int tc_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ldw, c
                      float* dx, int64_t lddx, int64_t M, int N, int K, cudaStream_t st);
 int tc_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx, float* dw, int64_t lddw, float* db,
                      int64_t M, int N, int K, cudaStream_t st);
+bool fused_bwd_eligible(const float* g, int64_t ldg, const float* h, int64_t ldh, const float* w, int64_t ldw,
+                        const float* dx, int64_t lddx, const float* dw, int64_t lddw, int64_t M, int N, int K);
+int tc_linear_bwd_fused(const float* g, int64_t ldg, const float* h, int64_t ldh, const float* w, int64_t ldw, int masked,
+                        float* dx, int64_t lddx, float* dw, int64_t lddw, float* db, int64_t M, cudaStream_t st);
 }  // namespace tc
 
 // skinny.cu: streaming kernels for layers with K <= 4 or N <= 4 (return 1 = handled, 0 = not applicable)
@@ -370,6 +374,20 @@ int npfk_rows_fold_sum(const float* g, int64_t ldg, float* out, int64_t ldo, int
     NPFK_LAUNCH(rows_fold_sum_kernel, grid_for(rows * N, 256), 256, 0, as_stream(stream), g, ldg, out, ldo, rows, reps,
                 N);
     return check_launch("rows_fold_sum");
+}
+
+
+int npfk_linear_bwd_fused(const float* g, int64_t ldg, const float* x, int64_t ldx, const float* w, int64_t ldw,
+                          int masked, float* dx, int64_t lddx, float* dw, int64_t lddw, float* db, int64_t M, int N,
+                          int K, int mode, void* stream) {
+    NPFK_REQUIRE(g && x && w && dx && dw, "linear_bwd_fused: null pointer");
+    NPFK_REQUIRE(mode == NPFK_MODE_FP32 || mode == NPFK_MODE_FAST, "linear_bwd_fused: unknown mode %d", mode);
+    if (M <= 0) return NPFK_OK;
+    if (mode == NPFK_MODE_FAST && tc::fused_bwd_eligible(g, ldg, x, ldx, w, ldw, dx, lddx, dw, lddw, M, N, K))
+        return tc::tc_linear_bwd_fused(g, ldg, x, ldx, w, ldw, masked, dx, lddx, dw, lddw, db, M, as_stream(stream));
+    int rc = npfk_linear_bwd_dw(g, ldg, x, ldx, dw, lddw, db, M, N, K, mode, stream);
+    if (rc != NPFK_OK) return rc;
+    return npfk_linear_bwd_dx(g, ldg, w, ldw, masked ? x : nullptr, masked ? ldx : 0, dx, lddx, M, N, K, mode, stream);
 }
 
 }  // extern "C"

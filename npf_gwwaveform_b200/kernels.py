@@ -163,16 +163,20 @@ class _LinearFn(Function):
         else:
             g = dy
         dx = dw = db = dres = None
-        if ctx.needs_input_grad[0]:
-            dx = torch.empty(*dy.shape[:-1], K, device=dy.device, dtype=torch.float32)
-            if M > 0:
-                LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wv), ldw, None, 0, _p(dx), K, M, N, K, ctx.mode, st)
         need_w = ctx.needs_input_grad[1]
         need_b = ctx.has_b and ctx.needs_input_grad[2]
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(*dy.shape[:-1], K, device=dy.device, dtype=torch.float32)
         if need_w or need_b:
             dw = torch.zeros(N, K, device=dy.device, dtype=torch.float32)
             db = torch.zeros(N, device=dy.device, dtype=torch.float32) if need_b else None
-            if M > 0:
+        if dx is not None and dw is not None and M > 0:
+            LIB.call("npfk_linear_bwd_fused", _p(g), N, _p(xv), ldx, _p(wv), ldw, 0, _p(dx), K, _p(dw), K, _p(db),
+                     M, N, K, ctx.mode, st)
+        elif M > 0:
+            if dx is not None:
+                LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wv), ldw, None, 0, _p(dx), K, M, N, K, ctx.mode, st)
+            if dw is not None:
                 LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(xv), ldx, _p(dw), K, _p(db), M, N, K, ctx.mode, st)
         if ctx.has_res and ctx.needs_input_grad[3]:
             if res_rows == M:
@@ -268,17 +272,26 @@ class _MlpChainFn(Function):
         for i in range(n_layers - 1, -1, -1):
             N, Kd, ldh, ldw, _ = dims[i]
             hin = acts[i]
-            if ctx.needs_input_grad[5 + 2 * i] or (has_b[i] and ctx.needs_input_grad[6 + 2 * i]):
+            need_w = ctx.needs_input_grad[5 + 2 * i] or (has_b[i] and ctx.needs_input_grad[6 + 2 * i])
+            need_dx = i > 0 or ctx.needs_input_grad[3]
+            masked = i > 0 or x_is_relu
+            dw = db = None
+            if need_w:
                 dw = torch.zeros(N, Kd, device=g.device, dtype=torch.float32)
                 db = torch.zeros(N, device=g.device, dtype=torch.float32) if has_b[i] else None
-                if M > 0:
-                    LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(hin), ldh, _p(dw), Kd, _p(db), M, N, Kd, mode, st)
                 grads_wb[2 * i], grads_wb[2 * i + 1] = dw, db
-            need_dx = i > 0 or ctx.needs_input_grad[3]
+            if need_w and need_dx and M > 0:
+                # one pass over g and the saved input: dgrad (+ ReLU mask from hin) and wgrad together
+                dx = torch.empty(M, Kd, device=g.device, dtype=torch.float32)
+                LIB.call("npfk_linear_bwd_fused", _p(g), N, _p(hin), ldh, _p(wvs[i]), ldw, int(masked), _p(dx), Kd,
+                         _p(dw), Kd, _p(db), M, N, Kd, mode, st)
+                g = dx
+                continue
+            if need_w and M > 0:
+                LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(hin), ldh, _p(dw), Kd, _p(db), M, N, Kd, mode, st)
             if not need_dx:
                 g = None
                 break
-            masked = i > 0 or x_is_relu
             dx = torch.empty(M, Kd, device=g.device, dtype=torch.float32)
             if M > 0:
                 LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wvs[i]), ldw, _p(hin) if masked else None, ldh if masked else 0,

@@ -69,6 +69,49 @@ def test_linear_fast(M, N, K, relu, res_mode):
         assert rel_err(rd.grad, rs.grad) < TOL
 
 
+@pytest.mark.parametrize("M,x_is_relu", [(128, False), (333, True), (20000, True), (148 * 128 * 2 + 77, False)])
+def test_mlp_chain_fast_fused_backward(M, x_is_relu):
+    """3-layer 128-wide ReLU chain: every layer's backward runs npfk_linear_bwd_fused (dgrad with the ReLU mask
+    taken from the saved input + wgrad + bias gradient in one tcgen05 kernel); float64 reference uses the
+    kernel's own activation pattern."""
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    g = torch.Generator().manual_seed(M)
+    x = torch.randn(M, 128, generator=g)
+    if x_is_relu:
+        x = torch.relu(x)
+    ws = [torch.randn(128, 128, generator=g) / math.sqrt(128) for _ in range(3)]
+    bs = [torch.randn(128, generator=g) * 0.1 for _ in range(3)]
+    dy = torch.randn(M, 128, generator=g)
+    xd = x.cuda().requires_grad_(True)
+    wd = [w.cuda().requires_grad_(True) for w in ws]
+    bd = [b.cuda().requires_grad_(True) for b in bs]
+    y = Kn.mlp_chain(xd, list(zip(wd, bd)), x_is_relu=x_is_relu)
+    y.backward(dy.cuda())
+
+    # activation pattern of the kernels (pre-activations within tf32 noise of zero may land on either side of the
+    # ReLU, and a flipped unit changes the gradient by O(1)): the same layers through Kn.linear expose h1, h2
+    with torch.no_grad():
+        h1 = Kn.linear(xd, wd[0], bd[0], relu=True)
+        h2 = Kn.linear(h1, wd[1], bd[1], relu=True)
+    masks = [(h1 > 0).double().cpu(), (h2 > 0).double().cpu()]
+    xs = x.double().requires_grad_(True)
+    wss = [w.double().requires_grad_(True) for w in ws]
+    bss = [b.double().requires_grad_(True) for b in bs]
+    h = xs
+    for i in range(3):
+        h = h @ wss[i].t() + bss[i]
+        if i < 2:
+            h = h * masks[i]
+    h.backward(dy.double())
+    assert rel_err(y, h) < TOL
+    gx = xs.grad * (x > 0).double() if x_is_relu else xs.grad
+    assert rel_err(xd.grad, gx) < 2 * TOL, ("dx", rel_err(xd.grad, gx))
+    for i in range(3):
+        assert rel_err(wd[i].grad, wss[i].grad) < 2 * TOL, (f"dw{i}", rel_err(wd[i].grad, wss[i].grad))
+        assert rel_err(bd[i].grad, bss[i].grad) < 2 * TOL, (f"db{i}", rel_err(bd[i].grad, bss[i].grad))
+
+
 def test_linear_fast_strided():
     """operands that are column slices of wider tensors (split r_z_merger, SetConv output with a density column)"""
     from npf_gwwaveform_b200 import kernels as Kn
