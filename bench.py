@@ -181,6 +181,72 @@ class ClockSampler:
         return out
 
 
+# ------------------------------------------------------------------------------------------ roofline
+# kernel family -> (C-ABI entry points timed with CUDA events on the launching stream, roofline that bounds it,
+#                   device kernel whose ncu --set full DRAM traffic is recorded in profiles/ncu_traffic.json)
+KERNEL_FAMILIES = {
+    "attention backward (tcgen05)": (["npfk_mha_bwd"], "tensor", "attn_bwd_tc_kernel"),
+    "attention forward (tcgen05)": (["npfk_mha_fwd"], "tensor", "attn_fwd_tc_kernel"),
+    "linear forward (tcgen05 GEMM + bias/residual/ReLU epilogue)": (["npfk_linear_fwd"], "hbm", "tc_gemm_nt_kernel<0>"),
+    "linear backward fused (dgrad + mask + wgrad)": (["npfk_linear_bwd_fused"], "hbm", "tc_linear_bwd_fused_kernel"),
+    "linear dgrad": (["npfk_linear_bwd_dx"], "hbm", "tc_gemm_nt_kernel<1>"),
+    "linear wgrad": (["npfk_linear_bwd_dw"], "hbm", "tc_gemm_tn_kernel"),
+    "residual + LayerNorm": (["npfk_add_layernorm_fwd", "npfk_add_layernorm_bwd"], "hbm", "add_layernorm_fwd_kernel"),
+    "Gaussian log-likelihood": (["npfk_gauss_nll_fwd", "npfk_gauss_nll_bwd"], "hbm", "gauss_nll_fwd_kernel"),
+    "SetConv grid->target": (["npfk_setconv_interp_fwd", "npfk_setconv_interp_bwd"], "hbm", "setconv_interp_fwd_kernel"),
+}
+
+
+def ncu_traffic():
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the hot kernels at the bench's own
+    shapes, from the committed `ncu --set full` capture (tools/ncu_targets.py -> profiles/ncu_traffic.json)."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f)
+    return {}
+
+
+def build_roofline(ksum, total_ms, args, pk, B, Nt):
+    """`roofline` object of the JSON line: the dominant kernel family (largest share of the timed step) against the
+    roofline that bounds it, plus the same figures for every other timed family under `families`."""
+    traffic = ncu_traffic() if args.workload == "attncnp_c2" else {}
+    fams = {}
+    for fam, (names, bound, dev_kernel) in KERNEL_FAMILIES.items():
+        ms = sum(ksum.get(n, {}).get("ms_total", 0.0) for n in names)
+        calls = sum(ksum.get(n, {}).get("calls", 0) for n in names)
+        if calls == 0:
+            continue
+        flops = sum(ksum.get(n, {}).get("flops_total", 0.0) for n in names)
+        nbytes = sum(ksum.get(n, {}).get("bytes_total", 0.0) for n in names)
+        tfs = flops / (ms * 1e-3) / 1e12
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        e = {"bound": bound, "launches_timed": calls, "avg_launch_ms": ms / calls, "ms_per_step": ms / args.steps,
+             "share_of_step": ms / total_ms, "device_kernel": dev_kernel}
+        if bound == "tensor":
+            # peak = measured dense bf16 (MEASURED_PEAKS.json); the kernels run kind::tf32, whose dense peak is half
+            e.update(achieved=tfs, peak=pk["tflops"], unit="TFLOP/s", frac=tfs / pk["tflops"],
+                     frac_of_tf32_peak=tfs / (pk["tflops"] / 2), flops_per_launch=flops / calls)
+        else:
+            e.update(achieved=gbs, peak=pk["hbm_gbs"], unit="GB/s", frac=gbs / pk["hbm_gbs"],
+                     algorithmic_bytes_per_launch=nbytes / calls, executed_tflops=tfs)
+        t = next((v for k, v in traffic.items() if k.startswith(dev_kernel)), None)
+        e["traffic"] = t["bytes_per_launch"] if t else None
+        if t:
+            e["traffic_note"] = t.get("note", "")
+        fams[fam] = e
+    if not fams:
+        return {"bound": "hbm", "achieved": None, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": None}
+    dom = max(fams, key=lambda f: fams[f]["share_of_step"])
+    out = {"kernel": dom}
+    out.update(fams[dom])
+    out["peak_source"] = pk["source"]
+    alg = 3 * FLOPS_FWD_PER_TARGET[args.workload] * B * Nt / (total_ms / args.steps * 1e-3) / 1e12
+    out["whole_step"] = {"algorithmic_tflops": alg, "frac_of_peak": alg / pk["tflops"]}
+    out["families"] = {f: e for f, e in fams.items() if f != dom}
+    return out
+
+
 # ------------------------------------------------------------------------------------------ product arm
 def run_ours(args):
     import torch
@@ -249,7 +315,7 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         step_resident()
-    timed_names = ["npfk_linear_fwd", "npfk_linear_bwd_dx", "npfk_linear_bwd_dw", "npfk_mha_fwd", "npfk_mha_bwd"]
+    timed_names = [n for ns in KERNEL_FAMILIES.values() for n in ns[0]]
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -274,24 +340,7 @@ def run_ours(args):
         return
 
     pk = peaks()
-    # dominant kernel family = the one with the largest share of the step
-    fam = {"sgemm (npfk_linear_fwd/bwd_dx/bwd_dw)": ["npfk_linear_fwd", "npfk_linear_bwd_dx", "npfk_linear_bwd_dw"],
-           "mha (npfk_mha_fwd/bwd)": ["npfk_mha_fwd", "npfk_mha_bwd"]}
-    fam_ms = {f: sum(ksum.get(n, {}).get("ms_total", 0.0) for n in ns) for f, ns in fam.items()}
-    dom = max(fam_ms, key=fam_ms.get)
-    dom_work = sum(ksum.get(n, {}).get("work_total", 0.0) for n in fam[dom])
-    dom_calls = sum(ksum.get(n, {}).get("calls", 0) for n in fam[dom])
-    achieved = dom_work / (fam_ms[dom] * 1e-3) / 1e12 if fam_ms[dom] > 0 else 0.0
-    roofline = {
-        "bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s",
-        "frac": achieved / pk["tflops"], "traffic": None, "peak_source": pk["source"],
-        "launches_timed": dom_calls, "avg_launch_ms": fam_ms[dom] / max(dom_calls, 1),
-        "share_of_step": fam_ms[dom] / total_ms,
-        "flops_per_launch": dom_work / max(dom_calls, 1),
-        "whole_step": {"algorithmic_tflops": 3 * FLOPS_FWD_PER_TARGET[args.workload] * B * Nt / (ms_per_step * 1e-3) / 1e12,
-                       "frac_of_peak": 3 * FLOPS_FWD_PER_TARGET[args.workload] * B * Nt / (ms_per_step * 1e-3) / 1e12 / pk["tflops"]},
-        "other_kernels_ms_per_step": {f: fam_ms[f] / args.steps for f in fam},
-    }
+    roofline = build_roofline(ksum, total_ms, args, pk, B, Nt)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -818,19 +818,46 @@ class KernelTimer:
         self._orig = None
 
     def _work(self, name, a):
-        # argument positions follow include/npfk.h
+        """(executed flops, algorithmic HBM bytes) of one call; argument positions follow include/npfk.h"""
         if name == "npfk_linear_fwd":
-            return 2.0 * a[10] * a[11] * a[12]
-        if name in ("npfk_linear_bwd_dx", "npfk_linear_bwd_dw"):
-            M, N, Kd = (a[8], a[9], a[10]) if name == "npfk_linear_bwd_dx" else (a[7], a[8], a[9])
-            return 2.0 * M * N * Kd
+            M, N, Kd = a[10], a[11], a[12]
+            res_rows = a[7] if a[5] else 0
+            return 2.0 * M * N * Kd, 4.0 * (M * Kd + M * N + (M * N if res_rows == M else 0))
+        if name == "npfk_linear_bwd_dx":
+            M, N, Kd = a[8], a[9], a[10]
+            return 2.0 * M * N * Kd, 4.0 * (M * N + M * Kd * (2 if a[4] else 1))
+        if name == "npfk_linear_bwd_dw":
+            M, N, Kd = a[7], a[8], a[9]
+            return 2.0 * M * N * Kd, 4.0 * (M * N + M * Kd)
+        if name == "npfk_linear_bwd_fused":
+            M, N, Kd = a[12], a[13], a[14]
+            return 4.0 * M * N * Kd, 4.0 * (M * N + 2 * M * Kd)
         if name == "npfk_mha_fwd":
             B, Nq, Nk, H, D = a[5:10]
-            return 4.0 * B * H * Nq * Nk * D
+            return 4.0 * B * H * Nq * Nk * D, 4.0 * B * H * D * (2 * Nq + 2 * Nk)
         if name == "npfk_mha_bwd":
             B, Nq, Nk, H, D = a[10:15]
-            return 14.0 * B * H * Nq * Nk * D      # dq pass: s, dp, dq (6) ; dkv pass: s, dp, dv, dk (8)
-        return 0.0
+            # S^T, dP^T, dV, dK, dQ: five GEMMs of 2*Nq*Nk*D each per (batch, head)
+            return 10.0 * B * H * Nq * Nk * D, 4.0 * B * H * D * (4 * Nq + 4 * Nk)
+        if name == "npfk_add_layernorm_fwd":
+            rows, C = a[7], a[8]
+            return 0.0, 4.0 * rows * C * (3 if a[1] else 2)
+        if name == "npfk_add_layernorm_bwd":
+            rows, C = a[9], a[10]
+            return 0.0, 4.0 * rows * C * (4 if a[2] else 3)
+        if name == "npfk_gauss_nll_fwd":
+            Z, B, T, yd = a[3:7]
+            return 0.0, 4.0 * (Z * B * T * 2 * yd + B * T * yd)
+        if name == "npfk_gauss_nll_bwd":
+            Z, B, T, yd = a[4:8]
+            return 0.0, 4.0 * (Z * B * T * 4 * yd + B * T * yd)
+        if name == "npfk_setconv_interp_fwd":
+            B, Nk, Nq, C = a[10:14]
+            return 0.0, 4.0 * B * (Nq * C + Nk * C + 3 * Nq)
+        if name == "npfk_setconv_interp_bwd":
+            B, Nk, Nq, C = a[13:17]
+            return 0.0, 4.0 * B * (Nq * C + 2 * Nk * C + 3 * Nq)
+        return 0.0, 0.0
 
     def __enter__(self):
         self._orig = LIB.call
@@ -842,7 +869,8 @@ class KernelTimer:
             e0.record()
             self._orig(name, *args)
             e1.record()
-            self.records.append((name, self._work(name, args), e0, e1))
+            flops, nbytes = self._work(name, args)
+            self.records.append((name, flops, nbytes, e0, e1))
 
         LIB.call = timed
         return self
@@ -851,13 +879,14 @@ class KernelTimer:
         LIB.call = self._orig
 
     def summary(self):
-        """{name: dict(calls, ms_total, ms_avg, work_total)} -- call after torch.cuda.synchronize()"""
+        """{name: dict(calls, ms_total, ms_avg, flops_total, bytes_total)} -- call after torch.cuda.synchronize()"""
         out = {}
-        for name, work, e0, e1 in self.records:
-            d = out.setdefault(name, dict(calls=0, ms_total=0.0, work_total=0.0))
+        for name, flops, nbytes, e0, e1 in self.records:
+            d = out.setdefault(name, dict(calls=0, ms_total=0.0, flops_total=0.0, bytes_total=0.0))
             d["calls"] += 1
             d["ms_total"] += e0.elapsed_time(e1)
-            d["work_total"] += work
+            d["flops_total"] += flops
+            d["bytes_total"] += nbytes
         for d in out.values():
             d["ms_avg"] = d["ms_total"] / max(d["calls"], 1)
         return out

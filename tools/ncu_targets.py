@@ -1,12 +1,18 @@
-"""Workload for `ncu --set full`: a few launches of the hot kernels at a reduced batch (64 tasks, 512/4096)."""
-import math, os, sys
+"""Workload for `ncu --set full`: two launches of each hot kernel at the bench's own shapes (C2: 256 tasks,
+512 context / 4096 target points, r_dim 128; C3 SetConv: 32 tasks, 192 grid points), fast (tf32) mode."""
+import math
+import os
+import sys
+
 ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
 sys.path.insert(0, ROOT)
-import torch
-import npf_gwwaveform_b200 as npf
-from npf_gwwaveform_b200 import kernels as Kn
+import torch  # noqa: E402
+
+import npf_gwwaveform_b200 as npf  # noqa: E402
+from npf_gwwaveform_b200 import kernels as Kn  # noqa: E402
+
 npf.set_mode("fast")
-B, Nq, Nk, H, D = 64, 4096, 512, 8, 16
+B, Nq, Nk, H, D = 256, 4096, 512, 8, 16
 E = H * D
 q, k, v, do = (torch.randn(B, n, E, device="cuda") for n in (Nq, Nk, Nk, Nq))
 for t in (q, k, v):
@@ -14,13 +20,39 @@ for t in (q, k, v):
 for _ in range(2):
     o = Kn.mha(q, k, v, H, 1 / math.sqrt(D))
     o.backward(do)
-x = torch.randn(B * Nq, 128, device="cuda", requires_grad=True)
+    q.grad = k.grad = v.grad = None
+del o
+# MLP chain on the target rows: forward GEMMs, fused backward (dgrad + mask + wgrad), first-layer wgrad
+x = q.detach().reshape(B * Nq, E).requires_grad_(True)
 w1 = (torch.randn(128, 128, device="cuda") * 0.05).requires_grad_(True)
 w2 = (torch.randn(128, 128, device="cuda") * 0.05).requires_grad_(True)
 b1 = torch.zeros(128, device="cuda", requires_grad=True)
+dy = do.reshape(B * Nq, E)
 for _ in range(2):
     y = Kn.mlp_chain(x, [(w1, b1), (w2, b1)])
-    y.sum().backward()
+    y.backward(dy)
+    x.grad = None
+del y
+# separate dgrad / wgrad kernels (shapes the fused kernel does not take still use them)
+xd = x.detach()
+for _ in range(2):
+    y = Kn.mlp_chain(xd, [(w1, b1)])          # wgrad only
+    y.backward(dy)
+dx = torch.empty_like(xd)
+from npf_gwwaveform_b200._lib import LIB  # noqa: E402
+
+st = torch.cuda.current_stream().cuda_stream
+wt = Kn.tf32_weight(w1)
+for _ in range(2):
+    LIB.call("npfk_linear_bwd_dx", dy.data_ptr(), 128, wt.data_ptr(), 128, xd.data_ptr(), 128, dx.data_ptr(), 128,
+             B * Nq, 128, 128, 1, st)
+# residual + LayerNorm
+g_, b_ = torch.ones(128, device="cuda", requires_grad=True), torch.zeros(128, device="cuda", requires_grad=True)
+for _ in range(2):
+    o = Kn.add_layernorm(x, dy, g_, b_)
+    o.backward(dy)
+    x.grad = None
+del o
 torch.cuda.synchronize()
 # SetConv induced -> target (C3 shape per task: 192 grid points, 4096 targets, 128 channels) and the Gaussian NLL
 Bs = 32

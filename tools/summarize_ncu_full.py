@@ -44,3 +44,19 @@ for r in rows:
     t = num(r, "gpu__time_duration.sum")
     out += [f"{traffic / 1e6:.2f}", f"{traffic / t / 1e9:.1f}"]
     w.writerow(out)
+
+# optional second argument: write {device kernel: {bytes_per_launch, time_ms, note}} for bench.py's `traffic`
+# (last captured launch of each kernel = warm caches)
+if len(sys.argv) > 2:
+    import json
+
+    tr = {}
+    for r in rows:
+        name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "").replace("npfk::", "").replace("tc::", "")
+        traffic = num(r, "dram__bytes_read.sum") + num(r, "dram__bytes_write.sum")
+        tr[name] = {"bytes_per_launch": traffic, "time_ms": num(r, "gpu__time_duration.sum") * 1e3,
+                    "dram_read": num(r, "dram__bytes_read.sum"), "dram_write": num(r, "dram__bytes_write.sum"),
+                    "note": "dram__bytes_read.sum + dram__bytes_write.sum of one launch under ncu --set full "
+                            "(tools/ncu_targets.py, bench shapes); writes still dirty in L2 at kernel end are not counted"}
+    with open(sys.argv[2], "w") as f:
+        json.dump(tr, f, indent=1, sort_keys=True)
