@@ -267,8 +267,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     const bool tail = (c == nc - 1) && tail_valid < kAKC;
                     float mx = -INFINITY;
                     if (!tail) {
+                        // four independent chains (a single running max is a 32-deep dependent FMNMX chain)
+                        float mq[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, fmaxf(__uint_as_float(v0[j]), __uint_as_float(v1[j])));
+                        for (int j = 0; j < 32; ++j)
+                            mq[j & 3] = fmaxf(mq[j & 3], fmaxf(__uint_as_float(v0[j]), __uint_as_float(v1[j])));
+                        mx = fmaxf(fmaxf(mq[0], mq[1]), fmaxf(mq[2], mq[3]));
                     } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
@@ -279,7 +283,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     const float m_new = fmaxf(m, mx);
                     const float mk = m_new * k2;
                     const float alpha = ex2_approx((m - m_new) * k2);      // m = -inf on the first chunk -> 0
-                    float ls = 0.f;
+                    float lq[4] = {0.f, 0.f, 0.f, 0.f};      // independent partial row sums (no 32-deep FADD chain)
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         // P is truncated to tf32 here (what the MMA would do anyway) so that the row sum l matches
@@ -292,9 +296,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         }
                         v0[j] = a;
                         v1[j] = bq;
-                        ls += __uint_as_float(a) + __uint_as_float(bq);
+                        lq[j & 3] += __uint_as_float(a) + __uint_as_float(bq);
                     }
-                    l = fmaf(l, alpha, ls);
+                    l = fmaf(l, alpha, (lq[0] + lq[1]) + (lq[2] + lq[3]));
                     m = m_new;
                     tmem_st_32x32(wg_base + sb * kAKC, v0);
                     tmem_st_32x32(wg_base + sb * kAKC + 32, v1);

@@ -156,6 +156,93 @@ __global__ void bcast_add_relu_bwd_dr_kernel(const float* __restrict__ dout, con
     }
 }
 
+// Vectorised variants for C % 4 == 0 (r_dim = 128).  Forward: a thread owns one float4 of a[b,t,:] and writes its
+// Z outputs (one index decomposition per thread instead of three 64-bit divisions per element).
+__global__ void __launch_bounds__(256)
+bcast_add_relu_fwd_v4_kernel(const float4* __restrict__ a, const float4* __restrict__ r, float4* __restrict__ out, int Z,
+                             int B, int64_t T, int C4) {
+    const int64_t btc4 = (int64_t)B * T * C4, tc4 = T * C4;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < btc4; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t bb = e / tc4;
+        const int c4 = (int)(e % C4);
+        const float4 av = __ldg(a + e);
+        const float4* rp = r + bb * C4 + c4;
+#pragma unroll 4
+        for (int z = 0; z < Z; ++z) {
+            const float4 rv = __ldg(rp + (int64_t)z * B * C4);
+            float4 o;
+            o.x = fmaxf(av.x + rv.x, 0.f);
+            o.y = fmaxf(av.y + rv.y, 0.f);
+            o.z = fmaxf(av.z + rv.z, 0.f);
+            o.w = fmaxf(av.w + rv.w, 0.f);
+            __stcs(out + (int64_t)z * btc4 + e, o);
+        }
+    }
+}
+
+// Backward in ONE pass over dout/out: CTA = (b, 64 consecutive t) x all z; thread = (t row of 8, float4 of channels).
+// da[b,t,:] = sum_z g accumulates in registers, dr[z,b,:] += sum_t g through a shared-memory reduction per z.
+constexpr int kBcTRows = 8, kBcTIter = 8;      // 64 positions per CTA
+__global__ void __launch_bounds__(256)
+bcast_add_relu_bwd_v4_kernel(const float4* __restrict__ dout, const float4* __restrict__ out, float4* __restrict__ da,
+                             float* __restrict__ dr, int Z, int B, int64_t T, int C4) {
+    __shared__ float4 red[kBcTRows][32];
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31, trow = threadIdx.x >> 5;
+    const int64_t t0 = (int64_t)blockIdx.x * (kBcTRows * kBcTIter);
+    const int64_t btc4 = (int64_t)B * T * C4;
+    for (int cb = 0; cb < C4; cb += 32) {
+        const int c4 = cb + lane;
+        const bool cok = c4 < C4;
+        float4 acc[kBcTIter];
+#pragma unroll
+        for (int i = 0; i < kBcTIter; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int z = 0; z < Z; ++z) {
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int i = 0; i < kBcTIter; ++i) {
+                const int64_t t = t0 + i * kBcTRows + trow;
+                if (cok && t < T) {
+                    const int64_t idx = (int64_t)z * btc4 + ((int64_t)b * T + t) * C4 + c4;
+                    const float4 o = __ldcs(out + idx), g = __ldcs(dout + idx);
+                    float4 m;
+                    m.x = o.x > 0.f ? g.x : 0.f;
+                    m.y = o.y > 0.f ? g.y : 0.f;
+                    m.z = o.z > 0.f ? g.z : 0.f;
+                    m.w = o.w > 0.f ? g.w : 0.f;
+                    acc[i].x += m.x; acc[i].y += m.y; acc[i].z += m.z; acc[i].w += m.w;
+                    s.x += m.x; s.y += m.y; s.z += m.z; s.w += m.w;
+                }
+            }
+            if (dr) {
+                red[trow][lane] = s;
+                __syncthreads();
+                if (trow == 0 && cok) {
+                    float4 tsum = red[0][lane];
+#pragma unroll
+                    for (int w = 1; w < kBcTRows; ++w) {
+                        const float4 v = red[w][lane];
+                        tsum.x += v.x; tsum.y += v.y; tsum.z += v.z; tsum.w += v.w;
+                    }
+                    float* dst = dr + (((int64_t)z * B + b) * C4 + c4) * 4;
+                    atomicAdd(dst, tsum.x);
+                    atomicAdd(dst + 1, tsum.y);
+                    atomicAdd(dst + 2, tsum.z);
+                    atomicAdd(dst + 3, tsum.w);
+                }
+                __syncthreads();
+            }
+        }
+        if (da && cok) {
+#pragma unroll
+            for (int i = 0; i < kBcTIter; ++i) {
+                const int64_t t = t0 + i * kBcTRows + trow;
+                if (t < T) da[((int64_t)b * T + t) * C4 + c4] = acc[i];
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------- mean over the set dimension
 // grid (B); 256 threads = 32 channel lanes x 8 row lanes
 __global__ void __launch_bounds__(256)
@@ -232,6 +319,14 @@ int npfk_bcast_add_relu_fwd(const float* a, const float* r, float* out, int Z, i
     NPFK_REQUIRE(a && r && out, "bcast_add_relu_fwd: null pointer");
     const int64_t total = (int64_t)Z * B * T * C;
     if (total <= 0) return NPFK_OK;
+    const bool v4 = (C % 4 == 0) && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(r) |
+                                      reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+    if (v4) {
+        NPFK_LAUNCH(bcast_add_relu_fwd_v4_kernel, ew_grid(total / Z / 4), 256, 0, as_stream(stream),
+                    reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(r),
+                    reinterpret_cast<float4*>(out), Z, B, T, C / 4);
+        return check_launch("bcast_add_relu_fwd_v4");
+    }
     NPFK_LAUNCH(bcast_add_relu_fwd_kernel, ew_grid(total), 256, 0, as_stream(stream), a, r, out, Z, B, T, C);
     return check_launch("bcast_add_relu_fwd");
 }
@@ -243,6 +338,15 @@ int npfk_bcast_add_relu_bwd(const float* dout, const float* out, float* da, floa
     if (btc * Z <= 0) return NPFK_OK;
     cudaStream_t st = as_stream(stream);
     int rc = NPFK_OK;
+    const bool v4 = (C % 4 == 0) && B <= 65535 &&
+                    ((reinterpret_cast<uintptr_t>(dout) | reinterpret_cast<uintptr_t>(out) |
+                      reinterpret_cast<uintptr_t>(da) | reinterpret_cast<uintptr_t>(dr)) & 15) == 0;
+    if (v4 && (da || dr)) {
+        dim3 grid((unsigned)ceil_div64(T, kBcTRows * kBcTIter), B);
+        NPFK_LAUNCH(bcast_add_relu_bwd_v4_kernel, grid, 256, 0, st, reinterpret_cast<const float4*>(dout),
+                    reinterpret_cast<const float4*>(out), reinterpret_cast<float4*>(da), dr, Z, B, T, C / 4);
+        return check_launch("bcast_add_relu_bwd_v4");
+    }
     if (da) {
         NPFK_LAUNCH(bcast_add_relu_bwd_da_kernel, ew_grid(btc), 256, 0, st, dout, out, da, Z, btc);
         rc = check_launch("bcast_add_relu_bwd_da");

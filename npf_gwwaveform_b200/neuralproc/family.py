@@ -104,7 +104,8 @@ class NeuralProcessFamily(nn.Module, abc.ABC):
 
     def _validate_inputs(self, X_cntxt, Y_cntxt, X_trgt, Y_trgt):
         """ValueError for features outside [-1,1], training mode only (base.py:241-247)."""
-        if self._pending_flag is not None:           # lazy mode: result of the previous forward
+        capturing = X_trgt.is_cuda and torch.cuda.is_current_stream_capturing()
+        if self._pending_flag is not None and not capturing:     # lazy mode: result of the previous forward
             flag, self._pending_flag = self._pending_flag, None
             if int(flag.item()):
                 raise ValueError("Features during training should be in [-1,1] (detected on the previous forward).")
@@ -114,8 +115,8 @@ class NeuralProcessFamily(nn.Module, abc.ABC):
         if X_cntxt.numel():
             K.range_flag(X_cntxt, flag)
         K.range_flag(X_trgt, flag)
-        if _cfg["lazy_validation"]:
-            self._pending_flag = flag
+        if _cfg["lazy_validation"] or capturing:     # inside a CUDA-graph capture nothing may synchronise:
+            self._pending_flag = flag                # the owner of the graph reads the flag after a replay
         elif int(flag.item()):
             raise ValueError(
                 f"Features during training should be in [-1,1]. {X_cntxt.min()} <= X_cntxt <= {X_cntxt.max()} ; "

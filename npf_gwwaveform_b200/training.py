@@ -100,7 +100,8 @@ class FlatAdamTrainer:
     def _make_hook(self, i: int):
         def hook(_param):
             self._fired.append(i)
-            if self.overlap and self._order is not None and self.bucket_last.get(self.bucket_of[i]) == i:
+            if (self.overlap and self._order is not None and not getattr(self, "_capturing", False)
+                    and self.bucket_last.get(self.bucket_of[i]) == i):
                 self._launch_bucket(self.bucket_of[i])
         return hook
 
@@ -147,6 +148,59 @@ class FlatAdamTrainer:
             self._scatter_state(self.exp_avg, m)
             self._scatter_state(self.exp_avg_sq, v)
         return loss.detach()
+
+    # ------------------------------------------------------------------ CUDA-graph step
+    def capture(self, batch: dict) -> None:
+        """Record forward + loss + backward of one step into a CUDA graph (static copies of ``batch``'s tensors;
+        every later batch must have the same shapes).  Call after at least two eager ``step`` calls (buffers laid
+        out, kernels' one-time host initialisation done).  The gradient all-reduce and Adam stay outside the graph:
+        Adam's bias correction takes the step number as a host scalar."""
+        assert self._order is not None, "run eager steps before capture()"
+        torch.cuda.synchronize()
+        self._static = {k: v.clone() for k, v in batch.items()}
+        self._capturing = True
+        self._graph = torch.cuda.CUDAGraph()
+        try:
+            with torch.cuda.graph(self._graph):
+                self.flat_grad.zero_()
+                out = self.model(**self._static)
+                loss = self.criterion(out, self._static["Y_trgt"])
+                loss.backward()
+                self._static_loss = loss.detach()
+        finally:
+            self._capturing = False
+        for p_idx, p in enumerate(self.params):
+            o, n = self.offsets[p_idx]
+            assert p.grad is not None and p.grad.data_ptr() == self.flat_grad.data_ptr() + 4 * o, \
+                "a gradient left the flat buffer during capture"
+        self._flag_dev = getattr(self.model, "_pending_flag", None)
+        if self._flag_dev is not None:
+            self.model._pending_flag = None
+            self._flag_host = torch.zeros(1, dtype=self._flag_dev.dtype).pin_memory()
+            self._flag_event = None
+
+    def step_graphed(self, batch: dict) -> torch.Tensor:
+        """One optimisation step replaying the captured graph: H2D/D2D copy of the batch into the static buffers,
+        graph replay, gradient all-reduce, Adam.  The [-1,1] range check of the reference (base.py:241-247) is
+        read back asynchronously and raised at most one step late."""
+        if self._flag_dev is not None and self._flag_event is not None and self._flag_event.query():
+            self._flag_event = None
+            if int(self._flag_host.item()):
+                raise ValueError("Features during training should be in [-1,1] (detected on an earlier step).")
+        for k, v in batch.items():
+            if v is not self._static[k]:
+                self._static[k].copy_(v, non_blocking=True)
+        self._graph.replay()
+        if self._flag_dev is not None and self._flag_event is None:
+            self._flag_host.copy_(self._flag_dev, non_blocking=True)
+            self._flag_event = torch.cuda.Event()
+            self._flag_event.record()
+        if self.world > 1:
+            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+        self.step_count += 1
+        self.adam_impl(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0],
+                       self.betas[1], self.eps, self.step_count, 1.0 / self.world)
+        return self._static_loss
 
     def _gather_state(self, flat):
         return {i: flat[o:o + n].clone() for i, (o, n) in self.offsets.items()}

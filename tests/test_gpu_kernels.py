@@ -83,7 +83,7 @@ def test_linear_strided_operands():
     check_grads(["dW", "dX"], [Wd.grad, Xd.grad], [Ws.grad, Xs.grad])
 
 
-@pytest.mark.parametrize("Z,B,T,C", [(1, 3, 17, 32), (4, 2, 300, 128), (2, 1, 1, 8)])
+@pytest.mark.parametrize("Z,B,T,C", [(1, 3, 17, 32), (4, 2, 300, 128), (2, 1, 1, 8), (3, 2, 70, 6), (5, 2, 129, 160)])
 def test_bcast_add_relu(Z, B, T, C):
     from npf_gwwaveform_b200 import kernels as Kn
 

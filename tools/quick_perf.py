@@ -16,6 +16,7 @@ name = sys.argv[1] if len(sys.argv) > 1 else "AttnCNP"
 B, Nc, Nt = (int(a) for a in sys.argv[2:5]) if len(sys.argv) > 4 else (32, 512, 4096)
 nz = int(sys.argv[5]) if len(sys.argv) > 5 else 1
 set_lazy_validation(True)
+npf.set_mode(os.environ.get("NPFK_MODE", "fast"))
 torch.manual_seed(0)
 m = build_product(name, 128, nz=nz).cuda().train()
 inp = {k: v.cuda() for k, v in chirp_batch(B, Nc, Nt, 0).items()}
