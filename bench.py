@@ -269,6 +269,8 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL prints its version banner (NCCL_DEBUG=VERSION/WARN/INFO) on stdout: keep stdout to the ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/npf_nccl_%h_%p.log")
         dist.init_process_group("nccl", device_id=dev)
 
     model_name, B, Nc, Nt, nz = WORKLOADS[args.workload]
