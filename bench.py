@@ -29,6 +29,9 @@ WORKLOADS = {
     "convcnp_c3": ("ConvCNP_unet", 32, 512, 4096, 1),
     "attnlnp_c4": ("AttnLNP", 16, 512, 4096, 32),
     "cnp_c1": ("CNP", 64, 64, 128, 1),
+    # BASELINE.json configs[4] (inference sweep, forward only; one resident chunk of the 1M-task sweep per step)
+    "attncnp_c5_infer": ("AttnCNP", 64, 512, 16384, 1),
+    "convcnp_c5_infer": ("ConvCNP_unet", 64, 512, 16384, 1),
 }
 WORKLOAD_TEXT = {
     "attncnp_c2": "BASELINE.json configs[1]: AttnCNP (transformer attender, r_dim=128) on synthetic 1D chirp waveforms, "
@@ -36,9 +39,14 @@ WORKLOAD_TEXT = {
     "convcnp_c3": "BASELINE.json configs[2]: ConvCNP 1D (SetConv + UNet, density 64) on chirps, 512/4096, 32 tasks per GPU",
     "attnlnp_c4": "BASELINE.json configs[3]: AttnLNP, 32 z-samples, ELBO, 512/4096, 16 tasks per GPU",
     "cnp_c1": "BASELINE.json configs[0]: CNP, batch 64, 64 context / 128 target",
+    "attncnp_c5_infer": "BASELINE.json configs[4]: batched inference, AttnCNP predicting 16384-sample waveforms from 512 "
+                        "context points, chunks of 64 tasks per GPU, no communication",
+    "convcnp_c5_infer": "BASELINE.json configs[4]: batched inference, ConvCNP (SetConv + UNet) predicting 16384-sample "
+                        "waveforms from 512 context points, chunks of 64 tasks per GPU, no communication",
 }
 # algorithmic forward FLOPs per target point; backward = 2x
-FLOPS_FWD_PER_TARGET = {"attncnp_c2": 616.2e3, "convcnp_c3": 280.7e3, "attnlnp_c4": 8.93e6, "cnp_c1": 316.8e3}
+FLOPS_FWD_PER_TARGET = {"attncnp_c2": 616.2e3, "convcnp_c3": 280.7e3, "attnlnp_c4": 8.93e6, "cnp_c1": 316.8e3,
+                        "attncnp_c5_infer": 597.0e3, "convcnp_c5_infer": 231.0e3}
 
 
 def parse():
@@ -76,7 +84,8 @@ def cpu_reference_rate(workload, seconds, warmup=1, min_iters=2, max_iters=50, c
     from util_models import build_product, chirp_batch
 
     model, B, Nc, Nt, nz = WORKLOADS[workload]
-    chunk = chunk or {"attncnp_c2": 4, "convcnp_c3": 2, "attnlnp_c4": 1, "cnp_c1": 64}[workload]
+    infer = workload.endswith("_infer")
+    chunk = chunk or {"attncnp_c2": 4, "convcnp_c3": 2, "attnlnp_c4": 1, "cnp_c1": 64}.get(workload, 1)
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
     torch.manual_seed(0)
@@ -94,7 +103,11 @@ def cpu_reference_rate(workload, seconds, warmup=1, min_iters=2, max_iters=50, c
         loss_fn = O.elbo_loss
 
     def one():
-        O.loss_and_grads(fwd, loss_fn, sd, args, inp["Y_trgt"], training=True, **kw)
+        if infer:
+            with torch.no_grad():
+                fwd(sd, **args, training=False, **kw)
+        else:
+            O.loss_and_grads(fwd, loss_fn, sd, args, inp["Y_trgt"], training=True, **kw)
 
     for _ in range(warmup):
         one()
@@ -105,7 +118,8 @@ def cpu_reference_rate(workload, seconds, warmup=1, min_iters=2, max_iters=50, c
         one()
         times.append(time.time() - t0)
     t = statistics.median(times)
-    desc = (f"{chunk}-task chunk of the workload ({Nc} context / {Nt} target, n_z={nz}), forward+loss+backward, "
+    desc = (f"{chunk}-task chunk of the workload ({Nc} context / {Nt} target, n_z={nz}), "
+            f"{'forward only (eval)' if infer else 'forward+loss+backward'}, "
             f"median of {len(times)} runs after {warmup} warm-up, torch {torch.__version__} CPU fp32, {threads} threads")
     return chunk * Nt / t, desc, threads, t * 1e3
 
@@ -119,7 +133,8 @@ def run_reference(args):
                                                max_iters=n_iters)
     model, B, Nc, Nt, nz = WORKLOADS[args.workload]
     line = {
-        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference",
+        "metric": "target-points/sec forward (batched inference)" if args.workload.endswith("_infer") else METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD_TEXT[args.workload], "sample": desc, "timing": "host wall clock"},
@@ -247,6 +262,136 @@ def build_roofline(ksum, total_ms, args, pk, B, Nt):
     out["whole_step"] = {"algorithmic_tflops": alg, "frac_of_peak": alg / pk["tflops"]}
     out["families"] = {f: e for f, e in fams.items() if f != dom}
     return out
+
+
+# ------------------------------------------------------------------------------------------ inference sweep (C5)
+def run_infer(args):
+    """Forward-only throughput of one resident chunk of tasks (eval mode, no autograd), replicas only: every rank
+    predicts its own chunk, nothing is exchanged.  The predictive mean/std stay on the device; the e2e leg copies the
+    inputs H2D and reads a per-task summary (mean predictive std, 4 B per task) back."""
+    import torch
+    import torch.distributed as dist
+
+    import npf_gwwaveform_b200 as npf
+    from npf_gwwaveform_b200 import kernels as Kn
+    from util_models import build_product, chirp_batch
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (product arm) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/npf_nccl_%h_%p.log")
+        dist.init_process_group("nccl", device_id=dev)
+    model_name, B, Nc, Nt, nz = WORKLOADS[args.workload]
+    if args.tasks_per_gpu:
+        B = args.tasks_per_gpu
+    npf.set_mode(args.mode)
+    torch.manual_seed(0)
+    model = build_product(model_name, 128, nz=nz).to(dev).eval()
+    host = {k: v.pin_memory() for k, v in chirp_batch(B, Nc, Nt, 1234 + rank).items() if k != "Y_trgt"}
+    static = {k: v.to(dev) for k, v in host.items()}
+    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
+    summary_host = torch.zeros(B).pin_memory()
+
+    def forward():
+        with torch.no_grad():
+            p = model(static["X_cntxt"], static["Y_cntxt"], static["X_trgt"])[0]
+            return p.base_dist.loc, p.base_dist.scale
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_loop(fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(args.warmup, 3)):
+        forward()
+    timed_names = [n for ns in KERNEL_FAMILIES.values() for n in ns[0]]
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    n0 = Kn.launch_count()
+    with Kn.KernelTimer(timed_names) as kt:
+        total_ms = timed_loop(forward, args.steps)
+    launches = Kn.launch_count() - n0
+    ksum = kt.summary()
+    eager_ms = total_ms / args.steps
+    ms_per_step = eager_ms
+    step = forward
+    use_graph = args.graph in ("on", "auto")
+    if use_graph:
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            g_loc, g_scale = forward()
+            g_summary = g_scale.mean(dim=(0, 2, 3))
+        step = graph.replay
+        for _ in range(3):
+            step()
+        ms_per_step = timed_loop(step, args.steps) / args.steps
+    clocks = sampler.stop() if rank == 0 else {}
+    value = world * B * Nt / (ms_per_step * 1e-3)
+
+    def step_e2e():
+        for k, v in host.items():
+            static[k].copy_(v, non_blocking=True)
+        if use_graph:
+            graph.replay()
+            summ = g_summary
+        else:
+            summ = forward()[1].mean(dim=(0, 2, 3))
+        summary_host.copy_(summ, non_blocking=False)
+
+    for _ in range(2):
+        step_e2e()
+    e2e_ms = timed_loop(step_e2e, args.steps) / args.steps
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    roofline = build_roofline(ksum, total_ms, args, pk, B, Nt)
+    alg = FLOPS_FWD_PER_TARGET[args.workload] * B * Nt / (ms_per_step * 1e-3) / 1e12
+    roofline["whole_step"] = {"algorithmic_tflops": alg, "frac_of_peak": alg / pk["tflops"]}
+    line = {
+        "metric": "target-points/sec forward (batched inference)", "value": value, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.mode == "fp32" else "tf32 operands (tcgen05 kind::tf32), f32 accumulate, f32 storage",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD_TEXT[args.workload], "tasks_per_gpu": B, "global_batch": B * world,
+                   "n_context": Nc, "n_target": Nt, "mode": args.mode,
+                   "step": "forward only (eval mode, no autograd): predictive mean and std of every target stay in HBM",
+                   "launch": "CUDA graph replay" if use_graph else "eager launches", "eager_ms_per_step": eager_ms,
+                   "parallelism": f"replicas x{world}, no communication",
+                   "l2": "activations streamed per step exceed the 126 MB L2; no explicit flush"},
+        "clocks": clocks,
+        "e2e": {"value": world * B * Nt / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                "h2d_bytes_per_step": h2d_bytes * world, "d2h_bytes_per_step": 4 * B * world,
+                "path": "pinned host inputs -> static device inputs -> model.forward (eval) -> per-task mean predictive "
+                        "std to host"},
+        "gpu_launches": launches, "roofline": roofline,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 # ------------------------------------------------------------------------------------------ product arm
@@ -397,6 +542,8 @@ def main():
     args = parse()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload.endswith("_infer"):
+        run_infer(args)
     else:
         run_ours(args)
 
