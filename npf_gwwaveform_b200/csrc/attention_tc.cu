@@ -16,6 +16,7 @@
 // the warpgroup folds O_c into its register accumulator, rescaled by exp2((m_old-m_new)*scale*log2e).
 // Single pass: every logit is computed and read once; nothing but q, k, v, out and lse touches HBM.
 #include <math.h>
+#include <stdlib.h>
 
 #include "tc_common.cuh"
 
@@ -46,6 +47,7 @@ struct AttnParams {
     int64_t Nq, Nk;
     float scale;
     int n_chunks, q_tiles, nsplit, tiles_per_split;
+    int stagger_ns;      // start-up delay of warpgroup 1 (de-phases the two softmax warpgroups on the MUFU pipe)
     int* g_abort;
 };
 
@@ -105,7 +107,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
         for (int i = 0; i < kAQSlots; ++i) {
             mbar_init(&bar.q_full[i], 1);
-            mbar_init(&bar.q_empty[i], 1);
+            mbar_init(&bar.q_empty[i], HB);     // one commit per unit (head) that reads the tile
         }
         for (int i = 0; i < 4; ++i) {
             mbar_init(&bar.s_full[i], 1);
@@ -162,7 +164,82 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             const uint64_t d_q0 = make_sdesc_sw128(smem_u32(base + kAQOff), 16, 1024);
             uint32_t cnt[2] = {0, 0};       // S / P / O buffer use counters per warpgroup
             uint32_t kv_it = 0;             // streamed K/V chunks consumed so far
+            // Resident K/V: the two warpgroups are served as two INDEPENDENT streams of (unit, chunk) steps.  Stream g
+            // always has S of its next two steps issued; when its P(n) is ready the issuer queues P.V(n) and then
+            // S(n+2) into the buffer P.V(n) has just read (the tensor pipe executes in order).  Nothing makes one
+            // warpgroup wait for the other, so their exp phases need not coincide on the MUFU pipe.
+            auto role_streams = [&]() {
+                for (int c = 0; c < nc; ++c)
+                    if (!mbar_wait(&bar.kv_full[c], 0, cta_abort, p.g_abort, 24)) return;
+                tc_fence_after();
+                uint32_t n_steps[2], s_issued[2] = {0, 0}, pv_done[2] = {0, 0};
+                for (int g = 0; g < 2; ++g) n_steps[g] = (uint32_t)((U - g + 1) / 2) * (uint32_t)nc;
+                auto issue_s = [&](int g, uint32_t n) -> bool {
+                    const int k = (int)(n / (uint32_t)nc), c = (int)(n % (uint32_t)nc);
+                    const int u = 2 * k + g, t = u / HB, hb = u % HB;
+                    const uint32_t qs = (uint32_t)t % kAQSlots;
+                    if (c == 0) {
+                        if (!mbar_wait(&bar.q_full[qs], ((uint32_t)t / kAQSlots) & 1, cta_abort, p.g_abort, 23)) return false;
+                        tc_fence_after();
+                    }
+                    const uint32_t ko = (uint32_t)(hb * D * 4);
+                    const uint64_t dq = sdesc_advance(d_q0, qs * kAQBytes + ko);
+                    const uint64_t dk = sdesc_advance(d_ring_k, (uint32_t)c * kASlotBytes + ko);
+                    const uint32_t tS = tmem_base + (uint32_t)g * kATmemWg + (n & 1) * kAKC;
+#pragma unroll
+                    for (int s = 0; s < D / 8; ++s)
+                        umma_tf32(tS, sdesc_advance(dq, s * 32), sdesc_advance(dk, s * 32), idesc_s, s > 0);
+                    umma_commit(&bar.s_full[g * 2 + (n & 1)]);
+                    return true;
+                };
+                for (int g = 0; g < 2; ++g)
+                    for (int i = 0; i < 2; ++i)
+                        if (s_issued[g] < n_steps[g]) {
+                            if (!issue_s(g, s_issued[g])) return;
+                            ++s_issued[g];
+                        }
+                uint32_t spin = 0;
+                while (pv_done[0] < n_steps[0] || pv_done[1] < n_steps[1]) {
+                    bool progressed = false;
+                    for (int g = 0; g < 2; ++g) {
+                        const uint32_t n = pv_done[g];
+                        if (n >= n_steps[g]) continue;
+                        if (!mbar_try_wait(smem_u32(&bar.p_ready[g * 2 + (n & 1)]), (n >> 1) & 1)) continue;
+                        tc_fence_after();
+                        const int k = (int)(n / (uint32_t)nc), c = (int)(n % (uint32_t)nc);
+                        const int u = 2 * k + g, t = u / HB, hb = u % HB;
+                        const uint32_t tP = tmem_base + (uint32_t)g * kATmemWg + (n & 1) * kAKC;
+                        const uint32_t tO = tmem_base + (uint32_t)g * kATmemWg + kATmemO + (n & 1) * 32;
+                        const uint64_t dv = sdesc_advance(d_ring_v, (uint32_t)c * kASlotBytes + ((D == 16) ? (uint32_t)hb * 64u : 0u));
+#pragma unroll
+                        for (int j = 0; j < kAKC / 8; ++j)
+                            umma_tf32_ts(tO, tP + 8 * j, sdesc_advance(dv, j * 1024), idesc_pv, j > 0);
+                        umma_commit(&bar.o_full[g * 2 + (n & 1)]);
+                        if (c == nc - 1) umma_commit(&bar.q_empty[(uint32_t)t % kAQSlots]);
+                        ++pv_done[g];
+                        if (s_issued[g] < n_steps[g]) {
+                            if (!issue_s(g, s_issued[g])) return;
+                            ++s_issued[g];
+                        }
+                        progressed = true;
+                    }
+                    if (progressed) {
+                        spin = 0;
+                    } else if ((++spin & 255u) == 255u) {
+                        if (*cta_abort) return;
+                        if (spin > kSpinLimit) {
+                            *cta_abort = 27;
+                            atomicCAS(p.g_abort, 0, 27);
+                            return;
+                        }
+                    }
+                }
+            };
             auto role = [&]() {
+                if (resident) {
+                    role_streams();
+                    return;
+                }
                 for (int pi = 0; pi < n_pairs; ++pi) {
                     const int ng = min(2, U - 2 * pi);
                     uint64_t dq[2];
@@ -217,7 +294,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     for (int g = 0; g < ng; ++g) {
                         cnt[g] += (uint32_t)nc;
                         const int u = 2 * pi + g, t = u / HB;
-                        if (HB == 1 || g == ng - 1) umma_commit(&bar.q_empty[(uint32_t)t % kAQSlots]);
+                        umma_commit(&bar.q_empty[(uint32_t)t % kAQSlots]);
                     }
                 }
             };
@@ -237,6 +314,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             return __all_sync(0xffffffffu, ok);
         };
         auto role = [&]() {
+            if (wg == 1 && p.stagger_ns > 0) __nanosleep((unsigned)p.stagger_ns);
             for (int u = wg; u < U; u += 2) {
                 const int t = u / HB, hb = u % HB;
                 const int64_t qrow = (int64_t)(qt_begin + t) * kAQT + row;
@@ -370,6 +448,14 @@ int attn_fwd_tc(const float* q, const float* k, const float* v, float* out, floa
     p.q_tiles = (int)((Nq + kAQT - 1) / kAQT);
     attn_split(p, B);
     p.g_abort = abort_flag_ptr();
+    {
+        static int stagger = -1;     // NPFK_ATTN_STAGGER_NS overrides the default (developer knob)
+        if (stagger < 0) {
+            const char* e = getenv("NPFK_ATTN_STAGGER_NS");
+            stagger = e ? atoi(e) : 600;
+        }
+        p.stagger_ns = stagger;
+    }
     static bool attr_done[2] = {false, false};
     const int di = D == 16 ? 0 : 1;
     if (!attr_done[di]) {
