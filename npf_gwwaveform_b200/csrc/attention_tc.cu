@@ -27,14 +27,14 @@ constexpr int kAQT = 128;                    // queries per tile (UMMA M, TMEM l
 constexpr int kAKC = 64;                     // keys per chunk (UMMA N of S, K of PV)
 constexpr int kARing = 8;                    // K/V ring slots
 constexpr int kAQSlots = 4;                  // Q tile slots
-constexpr int kAThreads = 320;
+constexpr int kAThreads = 448;                // TMA + MMA warps and up to three softmax warpgroups
 constexpr int kAKBytes = kAKC * 128;         // one chunk of a 32-float box
 constexpr int kASlotBytes = 2 * kAKBytes;    // K chunk + V chunk
 constexpr int kAQBytes = kAQT * 128;
 constexpr int kARingOff = 0;
 constexpr int kAQOff = kARing * kASlotBytes;             // 131072
 constexpr int kABarOff = kAQOff + kAQSlots * kAQBytes;   // 196608
-constexpr int kANumBars = 2 * kARing + 2 * kAQSlots + 12;
+constexpr int kANumBars = 2 * kARing + 2 * kAQSlots + 18;
 constexpr int kAFwdSmem = 1024 + kABarOff + kANumBars * 8 + 16;
 constexpr uint32_t kATmemCols = 512;         // per warpgroup: S 2 x 64 columns, O 2 x 32 columns (192), two warpgroups
 constexpr uint32_t kATmemWg = 192;
@@ -81,8 +81,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     bar.q_full = bars + 2 * kARing;
     bar.q_empty = bar.q_full + kAQSlots;
     bar.s_full = bar.q_empty + kAQSlots;
-    bar.p_ready = bar.s_full + 4;
-    bar.o_full = bar.s_full + 8;
+    bar.p_ready = bar.s_full + 6;
+    bar.o_full = bar.s_full + 12;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + kANumBars);
     volatile int* cta_abort = reinterpret_cast<volatile int*>(tmem_ptr + 1);
 
@@ -96,6 +96,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int U = n_qt * HB;                 // units = (query tile, head); unit u -> tile u / HB, head u % HB
     const int nc = p.n_chunks;
     const bool resident = nc <= kARing;
+    // Resident K/V with head dim 16: THREE softmax warpgroups (S 2 x 64 + O 2 x 16 = 160 TMEM columns each) so that
+    // three warps per scheduler share the MUFU pipe; otherwise two warpgroups of 192 columns.
+    const int nwg = (resident && D == 16) ? 3 : 2;
+    const uint32_t tm_wg = nwg == 3 ? 160u : kATmemWg;
+    const uint32_t o_str = nwg == 3 ? 16u : 32u;
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmQ);
@@ -109,7 +114,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             mbar_init(&bar.q_full[i], 1);
             mbar_init(&bar.q_empty[i], HB);     // one commit per unit (head) that reads the tile
         }
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < 6; ++i) {
             mbar_init(&bar.s_full[i], 1);
             mbar_init(&bar.p_ready[i], 4);
             mbar_init(&bar.o_full[i], 1);
@@ -172,11 +177,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 for (int c = 0; c < nc; ++c)
                     if (!mbar_wait(&bar.kv_full[c], 0, cta_abort, p.g_abort, 24)) return;
                 tc_fence_after();
-                uint32_t n_steps[2], s_issued[2] = {0, 0}, pv_done[2] = {0, 0};
-                for (int g = 0; g < 2; ++g) n_steps[g] = (uint32_t)((U - g + 1) / 2) * (uint32_t)nc;
+                uint32_t n_steps[3] = {0, 0, 0}, s_issued[3] = {0, 0, 0}, pv_done[3] = {0, 0, 0};
+                for (int g = 0; g < nwg; ++g) n_steps[g] = (uint32_t)((U - g + nwg - 1) / nwg) * (uint32_t)nc;
                 auto issue_s = [&](int g, uint32_t n) -> bool {
                     const int k = (int)(n / (uint32_t)nc), c = (int)(n % (uint32_t)nc);
-                    const int u = 2 * k + g, t = u / HB, hb = u % HB;
+                    const int u = nwg * k + g, t = u / HB, hb = u % HB;
                     const uint32_t qs = (uint32_t)t % kAQSlots;
                     if (c == 0) {
                         if (!mbar_wait(&bar.q_full[qs], ((uint32_t)t / kAQSlots) & 1, cta_abort, p.g_abort, 23)) return false;
@@ -185,31 +190,31 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     const uint32_t ko = (uint32_t)(hb * D * 4);
                     const uint64_t dq = sdesc_advance(d_q0, qs * kAQBytes + ko);
                     const uint64_t dk = sdesc_advance(d_ring_k, (uint32_t)c * kASlotBytes + ko);
-                    const uint32_t tS = tmem_base + (uint32_t)g * kATmemWg + (n & 1) * kAKC;
+                    const uint32_t tS = tmem_base + (uint32_t)g * tm_wg + (n & 1) * kAKC;
 #pragma unroll
                     for (int s = 0; s < D / 8; ++s)
                         umma_tf32(tS, sdesc_advance(dq, s * 32), sdesc_advance(dk, s * 32), idesc_s, s > 0);
                     umma_commit(&bar.s_full[g * 2 + (n & 1)]);
                     return true;
                 };
-                for (int g = 0; g < 2; ++g)
+                for (int g = 0; g < nwg; ++g)
                     for (int i = 0; i < 2; ++i)
                         if (s_issued[g] < n_steps[g]) {
                             if (!issue_s(g, s_issued[g])) return;
                             ++s_issued[g];
                         }
                 uint32_t spin = 0;
-                while (pv_done[0] < n_steps[0] || pv_done[1] < n_steps[1]) {
+                while (pv_done[0] < n_steps[0] || pv_done[1] < n_steps[1] || pv_done[2] < n_steps[2]) {
                     bool progressed = false;
-                    for (int g = 0; g < 2; ++g) {
+                    for (int g = 0; g < nwg; ++g) {
                         const uint32_t n = pv_done[g];
                         if (n >= n_steps[g]) continue;
                         if (!mbar_try_wait(smem_u32(&bar.p_ready[g * 2 + (n & 1)]), (n >> 1) & 1)) continue;
                         tc_fence_after();
                         const int k = (int)(n / (uint32_t)nc), c = (int)(n % (uint32_t)nc);
-                        const int u = 2 * k + g, t = u / HB, hb = u % HB;
-                        const uint32_t tP = tmem_base + (uint32_t)g * kATmemWg + (n & 1) * kAKC;
-                        const uint32_t tO = tmem_base + (uint32_t)g * kATmemWg + kATmemO + (n & 1) * 32;
+                        const int u = nwg * k + g, t = u / HB, hb = u % HB;
+                        const uint32_t tP = tmem_base + (uint32_t)g * tm_wg + (n & 1) * kAKC;
+                        const uint32_t tO = tmem_base + (uint32_t)g * tm_wg + kATmemO + (n & 1) * o_str;
                         const uint64_t dv = sdesc_advance(d_ring_v, (uint32_t)c * kASlotBytes + ((D == 16) ? (uint32_t)hb * 64u : 0u));
 #pragma unroll
                         for (int j = 0; j < kAKC / 8; ++j)
@@ -264,7 +269,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         for (int g = 0; g < ng; ++g) {
                             const uint32_t n = cnt[g] + (uint32_t)c, sb = n & 1;
                             const uint64_t dk = sdesc_advance(d_ring_k, slot * kASlotBytes + koff[g]);
-                            const uint32_t tS = tmem_base + (uint32_t)g * kATmemWg + sb * kAKC;
+                            const uint32_t tS = tmem_base + (uint32_t)g * tm_wg + sb * kAKC;
 #pragma unroll
                             for (int s = 0; s < D / 8; ++s)
                                 umma_tf32(tS, sdesc_advance(dq[g], s * 32), sdesc_advance(dk, s * 32), idesc_s, s > 0);
@@ -280,8 +285,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                             const uint32_t n = cnt[g] + (uint32_t)c, sb = n & 1;
                             if (!mbar_wait(&bar.p_ready[g * 2 + sb], (n >> 1) & 1, cta_abort, p.g_abort, 27)) return;
                             tc_fence_after();
-                            const uint32_t tP = tmem_base + (uint32_t)g * kATmemWg + sb * kAKC;
-                            const uint32_t tO = tmem_base + (uint32_t)g * kATmemWg + kATmemO + sb * 32;
+                            const uint32_t tP = tmem_base + (uint32_t)g * tm_wg + sb * kAKC;
+                            const uint32_t tO = tmem_base + (uint32_t)g * tm_wg + kATmemO + sb * o_str;
                             const uint64_t dv = sdesc_advance(d_ring_v, slot * kASlotBytes + voff[g]);
 #pragma unroll
                             for (int j = 0; j < kAKC / 8; ++j)
@@ -305,7 +310,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const int qd = warp & 3;                       // TMEM lane quarter of this warp
         const int wg = (warp - 2) >> 2;                // warpgroup = unit parity
         const int row = qd * 32 + lane;
-        const uint32_t wg_base = tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)wg * kATmemWg;
+        const uint32_t wg_base = tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)wg * tm_wg;
         const float k2 = p.scale * 1.4426950408889634f;
         const int tail_valid = (int)(p.Nk - (int64_t)(nc - 1) * kAKC);      // valid keys in the last chunk (1..64)
         uint32_t cnt = 0;
@@ -315,7 +320,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         };
         auto role = [&]() {
             if (wg == 1 && p.stagger_ns > 0) __nanosleep((unsigned)p.stagger_ns);
-            for (int u = wg; u < U; u += 2) {
+            for (int u = wg; u < U; u += nwg) {
                 const int t = u / HB, hb = u % HB;
                 const int64_t qrow = (int64_t)(qt_begin + t) * kAQT + row;
                 float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
@@ -327,8 +332,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     if (!wait_all(&bar.o_full[wg * 2 + (n & 1)], (n >> 1) & 1, 34)) return false;
                     tc_fence_after();
                     uint32_t r[D];
-                    if constexpr (D == 16) tmem_ld_32x16(wg_base + kATmemO + (n & 1) * 32, r);
-                    else tmem_ld_32x32(wg_base + kATmemO + (n & 1) * 32, r);
+                    if constexpr (D == 16) tmem_ld_32x16(wg_base + kATmemO + (n & 1) * o_str, r);
+                    else tmem_ld_32x32(wg_base + kATmemO + (n & 1) * o_str, r);
                     tmem_ld_wait();
 #pragma unroll
                     for (int d = 0; d < D; ++d) o[d] = fmaf(o[d], alpha, __uint_as_float(r[d]));
@@ -401,7 +406,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 }
             }
         };
-        if (U > 0) role();
+        if (U > 0 && wg < nwg) role();
     }
     tc_fence_before();
     __syncthreads();
