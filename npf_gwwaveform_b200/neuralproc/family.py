@@ -23,7 +23,7 @@ from ..utils.initialization import weights_init
 logger = logging.getLogger(__name__)
 
 __all__ = ["NeuralProcessFamily", "LatentNeuralProcessFamily", "CNP", "LNP", "AttnCNP", "AttnLNP", "ConvCNP",
-           "set_lazy_validation"]
+           "ConvLNP", "set_lazy_validation"]
 
 _cfg = {"lazy_validation": False}
 
@@ -421,3 +421,64 @@ class ConvCNP(NeuralProcessFamily):
     def set_extrapolation(self, min_max):
         lo, hi = min_max[0] - 0.5, min_max[1] + 0.5
         self.X_induced = torch.linspace(lo, hi, int(self.density_induced * (hi - lo)))
+
+
+class ConvLNP(LatentNeuralProcessFamily, ConvCNP):
+    """Convolutional latent NP (convnp.py:184-335): one latent per grid point, a second CNN after sampling
+    ("mixing" the samples), optional global latent, SetConv to the targets on the n_z * B batch.
+
+    Same constructor as the reference: ``CNNPostZ=None`` (defaults to ``CNN``), ``encoded_path`` in
+    {"latent", "both"}, ``is_global``, plus the ConvCNP / latent-family keyword arguments.  Every stage runs in the
+    npfk kernels already used by ConvCNP and the latent family (SetConv, conv blocks, latent statistics, rsample,
+    hoisted SetConv interpolation, skinny Linear decoder)."""
+
+    _valid_paths = ["latent", "both"]
+
+    def __init__(self, x_dim, y_dim, CNNPostZ=None, encoded_path="latent", is_global=False, **kwargs):
+        super().__init__(x_dim, y_dim, encoded_path=encoded_path, **kwargs)
+        self.is_global = is_global
+        if CNNPostZ is None:
+            CNNPostZ = self.CNN
+        self.induced_to_induced_post_sampling = CNNPostZ(self.r_dim)
+        self.reset_parameters()
+
+    @property
+    def dflt_Modules(self):
+        mods = ConvCNP.dflt_Modules.__get__(self)
+        mods.update(LatentNeuralProcessFamily.dflt_Modules.__get__(self))
+        # smaller decoder than ConvCNP: the representation already went through the post-sampling CNN
+        mods["Decoder"] = discard_ith_arg(nn.Linear, i=0)
+        return mods
+
+    def rep_to_lat_input(self, R):
+        if self.encoded_path == "latent":
+            return R                                         # one latent per induced point: [B, n_induced, r]
+        return K.set_mean(R.reshape(R.shape[0], -1, self.r_dim))    # "both": a global latent
+
+    def trgt_dependent_representation(self, X_cntxt, z_samples, R_induced, X_trgt):
+        B, n_trgt, _ = X_trgt.shape
+        n_z = z_samples.shape[0]
+        self.X_induced = self.X_induced.to(X_trgt.device)
+        X_induced = self.X_induced.view(1, -1, 1).expand(n_z * B, self.n_induced, self.x_dim)   # shared grid (stride 0)
+        X_trgt_rep = X_trgt.unsqueeze(0).expand(n_z, B, n_trgt, self.x_dim).reshape(n_z * B, n_trgt, self.x_dim)
+        if self.encoded_path == "latent":
+            z = z_samples.reshape(n_z * B, self.n_induced, self.z_dim)
+            if self.z_dim != self.r_dim:
+                z = K.linear(z, self.reshaper_z.weight, self.reshaper_z.bias)
+            z = self.induced_to_induced_post_sampling(z)    # mixing after sampling: coherent samples
+            if self.is_global:
+                z = self.add_global_latent(z)
+            R_trgt = self.induced_to_trgt(X_induced, X_trgt_rep, z)
+        else:
+            z = z_samples.expand(n_z, B, self.n_induced, self.z_dim)
+            R = self.merge_r_z(R_induced, z).reshape(n_z * B, self.n_induced, self.r_dim)
+            R = self.induced_to_induced_post_sampling(R)
+            R_trgt = self.induced_to_trgt(X_induced, X_trgt_rep, R)
+        return R_trgt.view(n_z, B, n_trgt, self.r_dim)
+
+    def add_global_latent(self, z_samples):
+        """second half of the channels := their mean over the grid (helpers.py:21-34 pool_and_replicate_middle)"""
+        half = z_samples.shape[-1] // 2
+        local, glob = z_samples.split(half, dim=-1)
+        glob = glob.mean(dim=1, keepdim=True).expand(-1, z_samples.shape[1], -1)
+        return torch.cat([local, glob], dim=-1)

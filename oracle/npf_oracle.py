@@ -190,11 +190,13 @@ def batch_norm(sd: SD, prefix: str, x: Tensor, training: bool, new_stats: Option
         mean = x.mean(dim=(0, 1))
         var = ((x - mean) ** 2).mean(dim=(0, 1))
         if new_stats is not None:
-            rm = sd[prefix + ".running_mean"].to(x.dtype)
-            rv = sd[prefix + ".running_var"].to(x.dtype)
-            new_stats[prefix + ".running_mean"] = (1 - momentum) * rm + momentum * mean
-            new_stats[prefix + ".running_var"] = (1 - momentum) * rv + momentum * var * n / max(n - 1, 1)
-            new_stats[prefix + ".num_batches_tracked"] = sd[prefix + ".num_batches_tracked"] + 1
+            # a module applied twice in one forward (ConvLNP encodes context and targets) updates its statistics twice
+            rm = new_stats.get(prefix + ".running_mean", sd[prefix + ".running_mean"]).to(x.dtype)
+            rv = new_stats.get(prefix + ".running_var", sd[prefix + ".running_var"]).to(x.dtype)
+            nb = new_stats.get(prefix + ".num_batches_tracked", sd[prefix + ".num_batches_tracked"])
+            new_stats[prefix + ".running_mean"] = ((1 - momentum) * rm + momentum * mean).detach()
+            new_stats[prefix + ".running_var"] = ((1 - momentum) * rv + momentum * var * n / max(n - 1, 1)).detach()
+            new_stats[prefix + ".num_batches_tracked"] = nb + 1
     else:
         mean = sd[prefix + ".running_mean"].to(x.dtype)
         var = sd[prefix + ".running_var"].to(x.dtype)
@@ -526,12 +528,60 @@ def attnlnp_forward(sd: SD, x_c: Tensor, y_c: Tensor, x_t: Tensor, y_t: Optional
     return out
 
 
+def convlnp_forward(sd: SD, x_c: Tensor, y_c: Tensor, x_t: Tensor, y_t: Optional[Tensor] = None,
+                    training: bool = False, n_z: int = 1, eps: Optional[Tensor] = None,
+                    density_induced: int = 64, encoded_path: str = "latent", is_global: bool = False,
+                    is_q_zCct: bool = True, new_stats: Optional[dict] = None) -> dict:
+    """ConvLNP (convnp.py:184-335 + base.py:374-575): latent per induced point, CNN after sampling, optional
+    global latent (neuralproc/helpers.py:21-34), SetConv on the n_z*B batch, decoder = DiscardIthArg(nn.Linear)."""
+    _check_range(training, x_c, x_t)
+    B, Nc, _ = x_c.shape
+    grid1 = torch.linspace(-1.5, 1.5, int(density_induced * 3)).to(x_c.dtype)
+    grid = grid1.view(1, -1, 1).expand(B, -1, 1)
+    U = grid.shape[1]
+    r_dim = sd["cntxt_to_induced.resizer.weight"].shape[0]
+
+    def encode(x, y):        # ConvCNP.encode_globally (convnp.py:128-154)
+        if x.shape[1] == 0:
+            R0 = torch.zeros(B, U, r_dim, dtype=x_t.dtype)
+        else:
+            R0 = set_conv(sd, "cntxt_to_induced", x, grid, y)
+        return cnn(sd, "induced_to_induced", R0, training, new_stats)
+
+    def lat_in(R):           # rep_to_lat_input (convnp.py:253-263)
+        return R if encoded_path == "latent" else R.reshape(B, -1, r_dim).mean(dim=1, keepdim=True)
+
+    R = encode(x_c, y_c)
+    out: dict = {}
+    r_ct = lat_in(encode(x_t, y_t)) if (is_q_zCct and y_t is not None) else None
+    z = _latent_path(sd, out, lat_in(R), r_ct, n_z, eps)             # [n_z, B, U or 1, z]
+    nz = z.shape[0]
+    gridz = grid1.view(1, -1, 1).expand(nz * B, -1, 1)
+    xt_rep = x_t.unsqueeze(0).expand(nz, *x_t.shape).reshape(nz * B, x_t.shape[1], 1)
+    if encoded_path == "latent":
+        h = z.reshape(nz * B, U, -1)
+        if "reshaper_z.weight" in sd:
+            h = linear(sd, "reshaper_z", h)
+        h = cnn(sd, "induced_to_induced_post_sampling", h, training, new_stats)
+        if is_global:
+            half = h.shape[-1] // 2
+            local, glob = h.split(half, dim=-1)
+            h = torch.cat([local, glob.mean(dim=1, keepdim=True).expand(-1, U, -1)], dim=-1)
+    else:
+        h = _merge_r_z(sd, R, z.expand(nz, B, U, z.shape[-1])).reshape(nz * B, U, r_dim)
+        h = cnn(sd, "induced_to_induced_post_sampling", h, training, new_stats)
+    r_trgt = set_conv(sd, "induced_to_trgt", gridz, xt_rep, h).view(nz, B, x_t.shape[1], r_dim)
+    out["loc"], out["scale"] = suffstat_to_loc_scale(linear(sd, "decoder.destination", r_trgt))
+    return out
+
+
 FORWARDS = {
     "CNP": cnp_forward,
     "AttnCNP": attncnp_forward,
     "ConvCNP": convcnp_forward,
     "LNP": lnp_forward,
     "AttnLNP": attnlnp_forward,
+    "ConvLNP": convlnp_forward,
 }
 
 

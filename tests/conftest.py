@@ -34,5 +34,5 @@ def load_golden(tag):
 GOLDEN_TAGS = [
     "cnp_r32", "attncnp_r32", "attncnp_multihead_r32", "attncnp_scaledot_r32", "convcnp_r32",
     "convcnp_unet_r32", "convcnp_unshared_r32", "lnp_r32", "lnp_both_r32", "attnlnp_r32", "attnlnp_nll_r32",
-    "attncnp_pretrained", "convcnp_pretrained",
+    "attncnp_pretrained", "convcnp_pretrained", "convlnp_nll_r32", "convlnp_both_r32",
 ]

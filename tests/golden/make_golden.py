@@ -26,7 +26,7 @@ sys.path.insert(0, REF)
 sys.dont_write_bytecode = True
 
 import npf  # noqa: E402  (the reference)
-from npf import CNP, LNP, AttnCNP, AttnLNP, ConvCNP, CNPFLoss, ELBOLossLNPF, NLLLossLNPF  # noqa: E402
+from npf import CNP, LNP, AttnCNP, AttnLNP, ConvCNP, ConvLNP, CNPFLoss, ELBOLossLNPF, NLLLossLNPF  # noqa: E402
 from npf.architectures import CNN, MLP, ResConvBlock, SetConv, UnetCNN, UnsharedExpRBF, discard_ith_arg, merge_flat_input  # noqa: E402
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -51,6 +51,13 @@ def build(name, R, **over):
         return AttnLNP(x_dim=1, y_dim=1, XYEncoder=xy(R), is_self_attn=False, is_q_zCct=True,
                        n_z_samples_train=over.get("nz", 3), n_z_samples_test=over.get("nz", 3), r_dim=R,
                        attention="transformer")
+    if name == "ConvLNP":        # ConvLNP.ipynb:150-200 (1-D): 4 ResConvBlocks, BatchNorm1d, Linear decoder
+        cnn = partial(CNN, ConvBlock=ResConvBlock, is_chan_last=True, n_conv_layers=2, n_blocks=4, Conv=torch.nn.Conv1d,
+                      Normalization=torch.nn.BatchNorm1d, kernel_size=over.get("kernel_size", 19))
+        return ConvLNP(x_dim=1, y_dim=1, Interpolator=SetConv, CNN=cnn, density_induced=over.get("density", 64),
+                       is_global=over.get("is_global", True), is_q_zCct=over.get("is_q_zCct", False),
+                       encoded_path=over.get("encoded_path", "latent"), n_z_samples_train=over.get("nz", 1),
+                       n_z_samples_test=over.get("nz", 1), r_dim=R, Decoder=discard_ith_arg(torch.nn.Linear, i=0))
     if name in ("ConvCNP", "ConvCNP_unet", "ConvCNP_unshared"):
         cnn_kw = dict(ConvBlock=ResConvBlock, is_chan_last=True, n_conv_layers=2, Conv=torch.nn.Conv1d,
                       Normalization=torch.nn.BatchNorm1d, n_blocks=5, kernel_size=over.get("kernel_size", 19))
@@ -97,7 +104,12 @@ def dist_fields(p):
     return p.base_dist.loc.detach().clone(), p.base_dist.scale.detach().clone()
 
 
+ONLY = [a for a in sys.argv[1:] if not a.startswith("-")]     # optional tag substrings: regenerate only those fixtures
+
+
 def run_case(tag, name, R, B, Nc, Nt, seed, loss_cls, nz=3, state=None, **over):
+    if ONLY and not any(f in tag for f in ONLY):
+        return
     torch.manual_seed(seed)
     model = build(name, R, nz=nz, **over)
     if state is not None:
@@ -105,13 +117,16 @@ def run_case(tag, name, R, B, Nc, Nt, seed, loss_cls, nz=3, state=None, **over):
     else:
         perturb(model, seed + 1)
     inp = chirp_inputs(B, Nc, Nt, seed + 2)
-    latent = name in ("LNP", "AttnLNP")
+    latent = name in ("LNP", "AttnLNP", "ConvLNP")
     fix = {"name": name, "r_dim": R, "kwargs": {k: v for k, v in over.items()}, "n_z": nz if latent else 1,
            "inputs": inp, "state_dict": {k: v.detach().clone() for k, v in model.state_dict().items()}}
 
     if latent:
         # G4: pin epsilon by patching rsample of the sampling distribution through a recorded draw
-        eps = torch.randn(nz, B, 1, R, generator=torch.Generator().manual_seed(seed + 3))
+        n_lat = 1
+        if name == "ConvLNP" and over.get("encoded_path", "latent") == "latent":
+            n_lat = int(over.get("density", 64) * 3)     # one latent per induced point
+        eps = torch.randn(nz, B, n_lat, R, generator=torch.Generator().manual_seed(seed + 3))
         fix["eps"] = eps
         orig = model.latent_path
 
@@ -142,7 +157,8 @@ def run_case(tag, name, R, B, Nc, Nt, seed, loss_cls, nz=3, state=None, **over):
     if latent:
         tr["z"] = z.detach().clone()
         tr["q_zCc_loc"], tr["q_zCc_scale"] = dist_fields(q_c)
-        tr["q_zCct_loc"], tr["q_zCct_scale"] = dist_fields(q_ct)
+        if q_ct is not None:
+            tr["q_zCct_loc"], tr["q_zCct_scale"] = dist_fields(q_ct)
     tr["grads"] = {k: v.grad.detach().clone() for k, v in model.named_parameters() if v.grad is not None}
     tr["state_after"] = {k: v.detach().clone() for k, v in model.state_dict().items() if "running_" in k or "num_batches" in k}
     fix["train"] = tr
@@ -177,6 +193,11 @@ def main():
     run_case("attnlnp_r32", "AttnLNP", R, 3, 9, 20, 50, ELBOLossLNPF, nz=3)
     run_case("attnlnp_nll_r32", "AttnLNP", R, 2, 6, 10, 51, NLLLossLNPF, nz=4)
 
+    run_case("convlnp_nll_r32", "ConvLNP", R, 2, 10, 24, 70, NLLLossLNPF, nz=3, density=16, kernel_size=5,
+             is_global=True, is_q_zCct=False)
+    run_case("convlnp_both_r32", "ConvLNP", R, 2, 10, 24, 71, ELBOLossLNPF, nz=2, density=16, kernel_size=5,
+             is_global=False, is_q_zCct=True, encoded_path="both")
+
     # reference's own trained weights at notebook width (fixtures for the headline model + BN statistics)
     pre = os.path.join(REF, "results/pretrained/RBF_Kernel")
     run_case("attncnp_pretrained", "AttnCNP", 128, 2, 16, 48, 60, CNPFLoss,
@@ -187,7 +208,13 @@ def main():
     # notebook-width layouts and parameter counts (known answers: CNP.ipynb:164, AttnCNP.ipynb:151,
     # ConvCNP.ipynb:164, LNP.ipynb:149, AttnLNP.ipynb:148) + C3's UNet
     layouts = {}
-    for nm in ["CNP", "AttnCNP", "ConvCNP", "ConvCNP_unet", "LNP", "AttnLNP"]:
+    lpath = os.path.join(HERE, "layouts.json")
+    if ONLY and os.path.exists(lpath):
+        with open(lpath) as f:
+            layouts = json.load(f)
+    for nm in ["CNP", "AttnCNP", "ConvCNP", "ConvCNP_unet", "LNP", "AttnLNP", "ConvLNP"]:
+        if ONLY and nm in layouts:
+            continue
         m = build(nm, 128, nz=1)
         layouts[nm] = {"n_params": sum(p.numel() for p in m.parameters()),
                        "state_dict": {k: list(v.shape) for k, v in m.state_dict().items()}}

@@ -16,7 +16,7 @@ def layouts():
         return json.load(f)
 
 
-@pytest.mark.parametrize("name", ["CNP", "AttnCNP", "ConvCNP", "ConvCNP_unet", "LNP", "AttnLNP"])
+@pytest.mark.parametrize("name", ["CNP", "AttnCNP", "ConvCNP", "ConvCNP_unet", "LNP", "AttnLNP", "ConvLNP"])
 def test_param_counts_and_state_dict_layout(name, layouts):
     # known answers: CNP.ipynb:164 (252,098), AttnCNP.ipynb:151 (252,738), ConvCNP.ipynb:164 (276,612),
     # LNP.ipynb:149 (301,634), AttnLNP.ipynb:148 (335,170); UNet variant 1,191,556
@@ -27,13 +27,14 @@ def test_param_counts_and_state_dict_layout(name, layouts):
 
 def test_known_param_counts(layouts):
     expect = {"CNP": 252098, "AttnCNP": 252738, "ConvCNP": 276612, "LNP": 301634, "AttnLNP": 335170,
-              "ConvCNP_unet": 1191556}
+              "ConvCNP_unet": 1191556, "ConvLNP": 376068}      # ConvLNP.ipynb:157
     for k, v in expect.items():
         assert layouts[k]["n_params"] == v
 
 
 @pytest.mark.parametrize("tag", ["cnp_r32", "attncnp_r32", "convcnp_r32", "convcnp_unet_r32", "convcnp_unshared_r32",
-                                 "lnp_r32", "lnp_both_r32", "attnlnp_r32", "attncnp_pretrained", "convcnp_pretrained"])
+                                 "lnp_r32", "lnp_both_r32", "attnlnp_r32", "attncnp_pretrained", "convcnp_pretrained",
+                                 "convlnp_nll_r32", "convlnp_both_r32"])
 def test_reference_state_dicts_load_strict(tag):
     fix = load_golden(tag)
     m = build_product(fix["name"], fix["r_dim"], nz=fix["n_z"], **fix["kwargs"])

@@ -25,11 +25,16 @@ def oracle_call(fix, training, with_y):
     fwd = O.FORWARDS[name if not name.startswith("ConvCNP") else "ConvCNP"]
     if name.startswith("ConvCNP"):
         extra = dict(density_induced=kw.get("density", 64), unet=name == "ConvCNP_unet")
+    if name == "ConvLNP":
+        extra = dict(n_z=fix["n_z"], eps=fix["eps"], density_induced=kw.get("density", 64),
+                     encoded_path=kw.get("encoded_path", "latent"), is_global=kw.get("is_global", True),
+                     is_q_zCct=kw.get("is_q_zCct", False))
+        args["y_t"] = inp["Y_trgt"] if with_y else None
     return fwd, args, extra
 
 
 def loss_for(fix):
-    if fix["name"] in ("LNP", "AttnLNP"):
+    if fix["name"] in ("LNP", "AttnLNP", "ConvLNP"):
         return O.nll_loss if "nll" in fix.get("tag", "") else O.elbo_loss
     return O.cnpf_loss
 
@@ -40,10 +45,10 @@ def test_oracle_matches_reference_train(tag):
     fix["tag"] = tag
     fwd, args, extra = oracle_call(fix, training=True, with_y=True)
     loss_fn = loss_for(fix)
-    if loss_fn is O.nll_loss:
-        loss_fn = lambda out, y: O.nll_loss(out, y, importance=True)  # noqa: E731  q_zCct given in training
+    if loss_fn is O.nll_loss:      # importance weights whenever q_zCct was inferred (losses.py:186-196)
+        loss_fn = lambda out, y: O.nll_loss(out, y, importance="q_zCct_loc" in out)  # noqa: E731
     new_stats = {}
-    if fix["name"].startswith("ConvCNP"):
+    if fix["name"].startswith("ConvCNP") or fix["name"] == "ConvLNP":
         extra["new_stats"] = new_stats
     inputs = {k: v for k, v in args.items() if torch.is_tensor(v)}
     rest = {k: v for k, v in args.items() if not torch.is_tensor(v)}
@@ -67,7 +72,7 @@ def test_oracle_matches_reference_train(tag):
     for k, v in ref["state_after"].items():
         if k in new_stats:
             torch.testing.assert_close(new_stats[k].to(v.dtype), v, rtol=1e-5, atol=1e-6)
-    if fix["name"].startswith("ConvCNP"):
+    if fix["name"].startswith("ConvCNP") or fix["name"] == "ConvLNP":
         assert set(new_stats) == set(ref["state_after"])
 
 

@@ -28,6 +28,13 @@ def build_product(name, R=128, nz=1, **over):
     if name == "AttnLNP":
         return npf.AttnLNP(x_dim=1, y_dim=1, XYEncoder=xy(R), is_self_attn=False, is_q_zCct=True,
                            n_z_samples_train=nz, n_z_samples_test=nz, r_dim=R, attention="transformer")
+    if name == "ConvLNP":        # ConvLNP.ipynb:150-200 (1-D)
+        cnn = partial(CNN, ConvBlock=ResConvBlock, is_chan_last=True, n_conv_layers=2, n_blocks=4, Conv=torch.nn.Conv1d,
+                      Normalization=torch.nn.BatchNorm1d, kernel_size=over.get("kernel_size", 19))
+        return npf.ConvLNP(x_dim=1, y_dim=1, Interpolator=SetConv, CNN=cnn, density_induced=over.get("density", 64),
+                           is_global=over.get("is_global", True), is_q_zCct=over.get("is_q_zCct", False),
+                           encoded_path=over.get("encoded_path", "latent"), n_z_samples_train=nz, n_z_samples_test=nz,
+                           r_dim=R, Decoder=discard_ith_arg(torch.nn.Linear, i=0))
     if name in ("ConvCNP", "ConvCNP_unet", "ConvCNP_unshared"):
         kw = dict(ConvBlock=ResConvBlock, is_chan_last=True, n_conv_layers=2, Conv=torch.nn.Conv1d,
                   Normalization=torch.nn.BatchNorm1d, n_blocks=5, kernel_size=over.get("kernel_size", 19))

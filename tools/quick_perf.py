@@ -20,7 +20,7 @@ npf.set_mode(os.environ.get("NPFK_MODE", "fast"))
 torch.manual_seed(0)
 m = build_product(name, 128, nz=nz).cuda().train()
 inp = {k: v.cuda() for k, v in chirp_batch(B, Nc, Nt, 0).items()}
-crit = (npf.ELBOLossLNPF if "LNP" in name else npf.CNPFLoss)().train()
+crit = (npf.NLLLossLNPF if name == "ConvLNP" else npf.ELBOLossLNPF if "LNP" in name else npf.CNPFLoss)().train()
 
 
 def step():
