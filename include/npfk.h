@@ -149,6 +149,16 @@ int npfk_setconv_interp_bwd(const float* xk, int64_t sxk, const float* xq, int64
                             float* dwd, float* dbias, float* dtheta, int B, int64_t Nk, int64_t Nq, int C, float p,
                             int unshared, void* stream);
 
+/* ---- context / target split on the device (npf/utils/datasplit.py:60-255) ------------------------
+ * idx:[B,n] int64 <- n distinct indices of [lo, lo+N) per task, uniform over subsets and orders (what
+ * GetRandomIndcs.__call__ draws with numpy on the host, datasplit.py:130-139); `shared` != 0: one draw for all
+ * tasks (is_batch_share).  Deterministic in (seed, task). N <= 57344. */
+int npfk_random_subset(int64_t* idx, int B, int N, int n, int64_t lo, int64_t seed, int shared, void* stream);
+/* dst[b,i,:] = src[b, idx[b,i], :]  (CntxtTrgtGetter.select, datasplit.py:246-255); src:[B,N,D] dst:[B,n,D].
+ * An index outside [0,N) writes zeros and sets *bad (may be NULL) instead of faulting. */
+int npfk_gather_rows(const float* src, const int64_t* idx, float* dst, int B, int64_t N, int64_t n, int D, int* bad,
+                     void* stream);
+
 /* ---- 1-D depth-separable residual conv blocks, channel-last [B,L,C] ------------------------------
  * Replaces BatchNorm1d -> ReLU -> Conv1d(groups=C) of ResConvBlock.forward (npf/architectures/cnn.py:
  * 204-215, npf/utils/helpers.py:395-398) without the NLC<->NCL permutes (cnn.py:363-375).

@@ -586,6 +586,22 @@ FORWARDS = {
 
 
 # --------------------------------------------------------------------------- #
+# context / target split  (npf/utils/datasplit.py)
+# --------------------------------------------------------------------------- #
+def select_points(X: Tensor, y: Tensor, indcs: Tensor) -> Tuple[Tensor, Tensor]:
+    """CntxtTrgtGetter.select (datasplit.py:246-255): gather rows of X and y by per-task indices."""
+    B = X.shape[0]
+    ix = indcs.unsqueeze(-1).expand(B, -1, X.shape[-1])
+    iy = indcs.unsqueeze(-1).expand(B, -1, y.shape[-1])
+    return torch.gather(X, 1, ix).contiguous(), torch.gather(y, 1, iy).contiguous()
+
+
+def add_cntxts_to_trgts(num_points: int, target_indcs: Tensor, context_indcs: Tensor) -> Tensor:
+    """CntxtTrgtGetter.add_cntxts_to_trgts (datasplit.py:229-237)."""
+    return torch.cat([target_indcs, context_indcs], dim=-1)[:, :num_points]
+
+
+# --------------------------------------------------------------------------- #
 # autograd helper: loss + parameter gradients through the oracle
 # --------------------------------------------------------------------------- #
 def loss_and_grads(forward, loss_fn, sd: SD, inputs: dict, y_trgt: Tensor, dtype=torch.float32, **kw):

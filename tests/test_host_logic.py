@@ -110,3 +110,22 @@ def test_cabi_rejects_bad_arguments_without_gpu():
     with pytest.raises(NpfkError, match="head size"):
         p = ctypes.c_void_p(16)
         LIB.call("npfk_mha_fwd", p, p, p, p, p, 1, 4, 4, 1, 5, 1.0, 0, None)
+
+
+def test_datasplit_host_rules():
+    """number-of-points rules of GetRandomIndcs (datasplit.py:106-126) and the no-host-path error"""
+    import random
+
+    from npf_gwwaveform_b200._lib import NpfkError
+    from npf_gwwaveform_b200.utils.datasplit import CntxtTrgtGetter, GetRandomIndcs, get_all_indcs
+
+    random.seed(0)
+    g = GetRandomIndcs(a=0.1, b=0.5)
+    assert all(10 <= g.n_indcs(100) <= 50 for _ in range(50))
+    assert GetRandomIndcs(a=0, b=0, is_ensure_one=True).n_indcs(10) == 1
+    assert GetRandomIndcs(a=7, b=7).n_indcs(10) == 7
+    assert get_all_indcs(3, 5).shape == (3, 5)
+    with pytest.raises(NpfkError):
+        CntxtTrgtGetter()(torch.zeros(2, 5, 1), torch.zeros(2, 5, 1))
+    with pytest.raises(NpfkError):
+        g(2, 10, device="cpu")
