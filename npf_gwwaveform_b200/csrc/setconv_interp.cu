@@ -91,17 +91,22 @@ __device__ __forceinline__ bool chunk_begin(const InterpArgs& a, int b, int64_t 
     return __syncthreads_or(qv && hit) != 0;
 }
 
+constexpr int kIPiece = 1024;   // keys staged in shared memory at a time (32 chunks)
+
+// Forward.  Per 1024-key piece the key positions are staged ONCE in shared memory together with the [min,max] interval
+// of each 32-key chunk; the chunk loop then costs one barrier per skipped chunk and touches global memory only for the
+// value rows of keys that matter (fetched four at a time, so their latencies overlap).
 __global__ void __launch_bounds__(kIThreads, 3)
 setconv_interp_fwd_kernel(const InterpArgs a, float* __restrict__ out, float* __restrict__ stats) {
     __shared__ __align__(16) float sW[kIK][kIQ];   // un-normalised weights of the current key chunk
-    __shared__ float sXk[kIK];
-    __shared__ int sAct[kIK];
-    __shared__ float sBnd[2];
-    __shared__ float sK[kIThreads];
+    __shared__ float sKeys[kIPiece];
+    __shared__ float sLo[kIPiece / kIK], sHi[kIPiece / kIK];
+    __shared__ unsigned sMask[2];                  // active keys of the chunk (bit j), double-buffered by chunk parity
     __shared__ float sRed[kIThreads];
     __shared__ float sInvL[kIQ];
     __shared__ float sDens[kIQ];
     const int b = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ql = threadIdx.x % kIQ, half = threadIdx.x / kIQ;
     const int64_t q0 = (int64_t)blockIdx.x * kIQ;
     const int nq = (int)min((int64_t)kIQ, a.Nq - q0);
@@ -109,9 +114,25 @@ setconv_interp_fwd_kernel(const InterpArgs a, float* __restrict__ out, float* __
     const float xq = qv ? __ldg(a.xq + (int64_t)b * a.sxq + q0 + ql) : 0.f;
     const float sigma = 1e-5f + softplus_f(__ldg(a.theta));
     const float sigma_d = a.unshared ? 1e-5f + softplus_f(__ldg(a.theta + 1)) : sigma;
+    const float* xkb = a.xk + (int64_t)b * a.sxk;
+    if (threadIdx.x < 2) sMask[threadIdx.x] = 0u;
 
+    // softmax stabiliser: inp at the nearest key (bit-identical to the maximum of inp over the keys)
     float m = 0.f;
-    if (!a.unshared) m = interp_inp_d(nearest_key_dist(a, b, xq, half, ql, sK, sRed), sigma, a.p);
+    if (!a.unshared) {
+        float dmin = CUDART_INF_F;
+        for (int64_t p0 = 0; p0 < a.Nk; p0 += kIPiece) {
+            const int np = (int)min((int64_t)kIPiece, a.Nk - p0);
+            __syncthreads();
+            for (int k = threadIdx.x; k < np; k += kIThreads) sKeys[k] = __ldg(xkb + p0 + k);
+            __syncthreads();
+            for (int jj = half; jj < np; jj += 2) dmin = fminf(dmin, fabsf(sKeys[jj] - xq));
+        }
+        __syncthreads();
+        sRed[threadIdx.x] = dmin;
+        __syncthreads();
+        m = interp_inp_d(fminf(sRed[ql], sRed[ql + kIQ]), sigma, a.p);
+    }
 
     for (int c0 = 0; c0 < a.C; c0 += kIC) {
         const int c = c0 + threadIdx.x;
@@ -119,39 +140,87 @@ setconv_interp_fwd_kernel(const InterpArgs a, float* __restrict__ out, float* __
 #pragma unroll
         for (int i = 0; i < kIQ; ++i) acc[i] = 0.f;
         float l = 0.f;   // sum of un-normalised weights (shared) or of the density terms (unshared), per (q, half)
-        for (int64_t k0 = 0; k0 < a.Nk; k0 += kIK) {
-            const int nk = (int)min((int64_t)kIK, a.Nk - k0);
-            if (!chunk_begin(a, b, k0, nk, xq, qv, m, sigma, sigma_d, sXk, sBnd, sAct)) continue;
-            for (int j = half; j < kIK; j += 2) {
-                float e = 0.f;
-                if (j < nk && qv) {
-                    const float d = fabsf(sXk[j] - xq);
-                    if (a.unshared) {
-                        const float i0 = interp_inp_d(d, sigma, a.p), i1 = interp_inp_d(d, sigma_d, a.p);
-                        e = expf(i0);
-                        l += expf(i1);
-                        if (fmaxf(i0, i1) > kCutUnshared) sAct[j] = 1;
-                    } else {
-                        const float i0 = interp_inp_d(d, sigma, a.p) - m;
-                        e = expf(i0);
-                        l += e;
-                        if (i0 > kCutShared) sAct[j] = 1;
-                    }
-                }
-                sW[j][ql] = e;
+        unsigned gen = 0;
+        for (int64_t p0 = 0; p0 < a.Nk; p0 += kIPiece) {
+            const int np = (int)min((int64_t)kIPiece, a.Nk - p0);
+            const int nch = (np + kIK - 1) / kIK;
+            if (a.Nk > kIPiece || a.unshared || c0 > 0 || p0 > 0) {     // otherwise sKeys still holds this piece
+                __syncthreads();
+                for (int k = threadIdx.x; k < np; k += kIThreads) sKeys[k] = __ldg(xkb + p0 + k);
             }
             __syncthreads();
-            if (c < a.C) {
-                for (int j = 0; j < nk; ++j) {
-                    if (!sAct[j]) continue;
-                    const float vv = __ldg(a.v + ((int64_t)b * a.Nk + k0 + j) * a.C + c);
+            for (int ch = warp; ch < nch; ch += kIThreads / 32) {       // [min,max] of every chunk of the piece
+                const bool ok = ch * kIK + lane < np;
+                const float x = ok ? sKeys[ch * kIK + lane] : 0.f;
+                float lo = ok ? x : CUDART_INF_F, hi = ok ? x : -CUDART_INF_F;
 #pragma unroll
-                    for (int i = 0; i < kIQ; i += 4) {
-                        const float4 w4 = *reinterpret_cast<const float4*>(&sW[j][i]);
-                        acc[i] = fmaf(w4.x, vv, acc[i]);
-                        acc[i + 1] = fmaf(w4.y, vv, acc[i + 1]);
-                        acc[i + 2] = fmaf(w4.z, vv, acc[i + 2]);
-                        acc[i + 3] = fmaf(w4.w, vv, acc[i + 3]);
+                for (int o = 16; o > 0; o >>= 1) {
+                    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+                    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+                }
+                if (lane == 0) {
+                    sLo[ch] = lo;
+                    sHi[ch] = hi;
+                }
+            }
+            __syncthreads();
+            for (int ch = 0; ch < nch; ++ch) {
+                const float dq = fmaxf(0.f, fmaxf(sLo[ch] - xq, xq - sHi[ch]));
+                bool hit;
+                if (a.unshared) hit = fmaxf(interp_inp_d(dq, sigma, a.p), interp_inp_d(dq, sigma_d, a.p)) > kCutUnshared;
+                else hit = interp_inp_d(dq, sigma, a.p) - m > kCutShared;
+                // the barrier also orders the previous chunk's value phase before sW is rewritten
+                if (!__syncthreads_or(qv && hit)) continue;
+                const int nk = min(kIK, np - ch * kIK);
+                const float* ck = sKeys + ch * kIK;
+                unsigned bits = 0u;
+                for (int jj = half; jj < kIK; jj += 2) {
+                    float e = 0.f;
+                    if (jj < nk && qv) {
+                        const float d = fabsf(ck[jj] - xq);
+                        if (a.unshared) {
+                            const float i0 = interp_inp_d(d, sigma, a.p), i1 = interp_inp_d(d, sigma_d, a.p);
+                            e = expf(i0);
+                            l += expf(i1);
+                            if (fmaxf(i0, i1) > kCutUnshared) bits |= 1u << jj;
+                        } else {
+                            const float i0 = interp_inp_d(d, sigma, a.p) - m;
+                            e = expf(i0);
+                            l += e;
+                            if (i0 > kCutShared) bits |= 1u << jj;
+                        }
+                    }
+                    sW[jj][ql] = e;
+                }
+                ++gen;
+                bits = __reduce_or_sync(0xffffffffu, bits);
+                if (lane == 0 && bits) atomicOr(&sMask[gen & 1], bits);
+                __syncthreads();
+                unsigned mask = sMask[gen & 1];
+                if (threadIdx.x == 0) sMask[(gen + 1) & 1] = 0u;       // the other buffer: read before this barrier
+                if (c < a.C) {
+                    const float* vb = a.v + ((int64_t)b * a.Nk + p0 + ch * kIK) * a.C + c;
+                    while (mask) {
+                        int jx[4];
+                        float vv[4];
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            jx[t] = mask ? __ffs(mask) - 1 : -1;
+                            if (mask) mask &= mask - 1;
+                            vv[t] = jx[t] >= 0 ? __ldg(vb + (int64_t)jx[t] * a.C) : 0.f;
+                        }
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            if (jx[t] < 0) break;
+#pragma unroll
+                            for (int i = 0; i < kIQ; i += 4) {
+                                const float4 w4 = *reinterpret_cast<const float4*>(&sW[jx[t]][i]);
+                                acc[i] = fmaf(w4.x, vv[t], acc[i]);
+                                acc[i + 1] = fmaf(w4.y, vv[t], acc[i + 1]);
+                                acc[i + 2] = fmaf(w4.z, vv[t], acc[i + 2]);
+                                acc[i + 3] = fmaf(w4.w, vv[t], acc[i + 3]);
+                            }
+                        }
                     }
                 }
             }
@@ -184,7 +253,7 @@ setconv_interp_fwd_kernel(const InterpArgs a, float* __restrict__ out, float* __
             float* op = out + ((int64_t)b * a.Nq + q0) * a.C + c;
 #pragma unroll
             for (int i = 0; i < kIQ; ++i)
-                if (i < nq) op[(int64_t)i * a.C] = fmaf(acc[i], sInvL[i], fmaf(sDens[i], wdc, bc));
+                if (i < nq) __stcs(op + (int64_t)i * a.C, fmaf(acc[i], sInvL[i], fmaf(sDens[i], wdc, bc)));
         }
     }
 }
