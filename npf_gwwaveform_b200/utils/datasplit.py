@@ -80,6 +80,12 @@ class GetRandomIndcs:
         self.seed = int(torch.initial_seed() if seed is None else seed) & 0x7FFFFFFFFFFFFFFF
         self.n_calls = 0
 
+    def reseed(self, seed):
+        """restart the device stream (eval_loglike does this so that every evaluation sees the same context sets,
+        like ``set_seed`` in utils/evaluate.py:11)"""
+        self.seed = int(seed) & 0x7FFFFFFFFFFFFFFF
+        self.n_calls = 0
+
     def n_indcs(self, n_possible_points):
         """number of indices of this call: host-side draw, same rules as datasplit.py:106-126"""
         if np.random.uniform(size=1) < self.proba_uniform:
@@ -188,4 +194,5 @@ def cntxt_trgt_collate(get_cntxt_trgt, is_duplicate_batch=False, device="cuda", 
         inputs = dict(X_cntxt=X_cntxt, Y_cntxt=Y_cntxt, X_trgt=X_trgt, Y_trgt=Y_trgt)
         return inputs, Y_trgt
 
+    mycollate.get_cntxt_trgt = get_cntxt_trgt
     return mycollate
