@@ -130,7 +130,8 @@ int npfk_add_layernorm_bwd(const float* dout, const float* a, const float* b, co
 int npfk_setconv_fwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq, const float* v,
                      const float* theta, float* out, int64_t ldo, int B, int64_t Nk, int64_t Nq, int C, float p,
                      int unshared, void* stream);
-/* dv:[B,Nk,C] "+=" ; dtheta:[1 or 2] "+=" ; positions get no gradient (they are data). */
+/* dv:[B,Nk,C] "+=" ; dtheta:[1 or 2] "+=" ; positions get no gradient (they are data).
+ * dv may be NULL when C <= 4 (the values are data too, as for the context set): only dtheta is computed. */
 int npfk_setconv_bwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq, const float* v,
                      const float* theta, const float* out, const float* dout, int64_t ldo, float* dv,
                      float* dtheta, int B, int64_t Nk, int64_t Nq, int C, float p, int unshared, void* stream);

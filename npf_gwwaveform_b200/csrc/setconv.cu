@@ -288,6 +288,127 @@ setconv_bwd_kernel(const SetConvArgs a, const float* __restrict__ out, const flo
     }
 }
 
+// ---- few value channels (context -> grid: C = y_dim, usually 1).  The tiled kernels above spend their time staging
+// 128-channel tiles that are almost empty; here one warp owns one (task, query), its lanes stride over the keys
+// (coalesced, L1-resident across the CTA's warps) and warp shuffles finish the sums.  No shared-memory tiles.
+constexpr int kSmallC = 4;
+constexpr int kSmallWarps = 8;
+
+template <int C>
+__global__ void __launch_bounds__(kSmallWarps * 32)
+setconv_small_fwd_kernel(const SetConvArgs a, float* __restrict__ out, int64_t ldo) {
+    const int b = blockIdx.y, lane = threadIdx.x & 31;
+    const int64_t q = (int64_t)blockIdx.x * kSmallWarps + (threadIdx.x >> 5);
+    if (q >= a.Nq) return;
+    const float xq = __ldg(a.xq + (int64_t)b * a.sxq + q);
+    const float sigma = 1e-5f + softplus_f(__ldg(a.theta));
+    const float sigma_d = a.unshared ? 1e-5f + softplus_f(__ldg(a.theta + 1)) : sigma;
+    const float* xk = a.xk + (int64_t)b * a.sxk;
+    const float* v = a.v + (int64_t)b * a.Nk * C;
+    float m = 0.f;
+    if (!a.unshared) {
+        m = -CUDART_INF_F;
+        for (int64_t k = lane; k < a.Nk; k += 32) m = fmaxf(m, rbf_inp(__ldg(xk + k), xq, sigma, a.p));
+        m = warp_max(m);
+    }
+    float l = 0.f, acc[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = 0.f;
+    for (int64_t k = lane; k < a.Nk; k += 32) {
+        const float x = __ldg(xk + k);
+        const float e = expf(rbf_inp(x, xq, sigma, a.p) - m);
+        l += a.unshared ? expf(rbf_inp(x, xq, sigma_d, a.p)) : e;
+#pragma unroll
+        for (int c = 0; c < C; ++c) acc[c] = fmaf(e, __ldg(v + k * C + c), acc[c]);
+    }
+    l = warp_sum(l);
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = warp_sum(acc[c]);
+    if (lane == 0) {
+        float* o = out + ((int64_t)b * a.Nq + q) * ldo;
+        const float inv = a.unshared ? 1.f / (l + 1e-8f) : 1.f / l;
+#pragma unroll
+        for (int c = 0; c < C; ++c) o[c] = acc[c] * inv;
+        o[C] = a.unshared ? l : l * expf(m);
+    }
+}
+
+// gradient of the length scale(s) only (the values are data: dv == nullptr)
+template <int C>
+__global__ void __launch_bounds__(kSmallWarps * 32)
+setconv_small_bwd_kernel(const SetConvArgs a, const float* __restrict__ out, const float* __restrict__ dout,
+                         int64_t ldo, float* __restrict__ dtheta) {
+    __shared__ float sRed[2][kSmallWarps];
+    const int b = blockIdx.y, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t q = (int64_t)blockIdx.x * kSmallWarps + wid;
+    const float th0 = __ldg(a.theta);
+    const float sigma = 1e-5f + softplus_f(th0);
+    const float th1 = a.unshared ? __ldg(a.theta + 1) : th0;
+    const float sigma_d = a.unshared ? 1e-5f + softplus_f(th1) : sigma;
+    float dsig0 = 0.f, dsig1 = 0.f;
+    if (q < a.Nq) {
+        const float xq = __ldg(a.xq + (int64_t)b * a.sxq + q);
+        const float* xk = a.xk + (int64_t)b * a.sxk;
+        const float* v = a.v + (int64_t)b * a.Nk * C;
+        const float* orow = out + ((int64_t)b * a.Nq + q) * ldo;
+        const float* drow = dout + ((int64_t)b * a.Nq + q) * ldo;
+        float dT[C], dot = 0.f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            dT[c] = __ldg(drow + c);
+            dot = fmaf(dT[c], __ldg(orow + c), dot);
+        }
+        const float ddens = __ldg(drow + C);
+        float m = 0.f, l = 0.f;
+        if (!a.unshared) {
+            m = -CUDART_INF_F;
+            for (int64_t k = lane; k < a.Nk; k += 32) m = fmaxf(m, rbf_inp(__ldg(xk + k), xq, sigma, a.p));
+            m = warp_max(m);
+        }
+        for (int64_t k = lane; k < a.Nk; k += 32)
+            l += expf(rbf_inp(__ldg(xk + k), xq, a.unshared ? sigma_d : sigma, a.p) - m);
+        l = warp_sum(l);
+        const float inv_l = a.unshared ? 1.f / (l + 1e-8f) : 1.f / l;
+        const float emax = a.unshared ? 1.f : expf(m);
+        const float dD = a.unshared ? ddens - dot * inv_l : 0.f;
+        for (int64_t k = lane; k < a.Nk; k += 32) {
+            const float x = __ldg(xk + k);
+            const float inp = rbf_inp(x, xq, sigma, a.p);
+            float dp = 0.f;
+#pragma unroll
+            for (int c = 0; c < C; ++c) dp = fmaf(dT[c], __ldg(v + k * C + c), dp);
+            if (a.unshared) {
+                const float w = expf(inp) * inv_l;
+                dsig0 += (dp * w) * (-a.p * inp / sigma);
+                const float inp1 = rbf_inp(x, xq, sigma_d, a.p);
+                dsig1 += (dD * expf(inp1)) * (-a.p * inp1 / sigma_d);
+            } else {   // same split as setconv_bwd_kernel: softmax part against (inp - m), density part against inp
+                const float e = expf(inp - m);
+                const float ds = e * inv_l * (dp - dot);
+                const float dd = ddens * e * emax;
+                dsig0 += (ds * (inp - m) + dd * inp) * (-a.p / sigma);
+            }
+        }
+    }
+    dsig0 = warp_sum(dsig0);
+    dsig1 = warp_sum(dsig1);
+    if (lane == 0) {
+        sRed[0][wid] = dsig0;
+        sRed[1][wid] = dsig1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t0 = 0.f, t1 = 0.f;
+#pragma unroll
+        for (int i = 0; i < kSmallWarps; ++i) {
+            t0 += sRed[0][i];
+            t1 += sRed[1][i];
+        }
+        atomicAdd(dtheta, t0 * sigmoid_f(th0));
+        if (a.unshared) atomicAdd(dtheta + 1, t1 * sigmoid_f(th1));
+    }
+}
+
 }  // namespace npfk
 
 using namespace npfk;
@@ -303,6 +424,16 @@ int npfk_setconv_fwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq,
     NPFK_REQUIRE(ldo >= C + 1, "setconv_fwd: ldo=%lld < C+1", (long long)ldo);
     NPFK_REQUIRE(p > 0.f, "setconv_fwd: p must be positive");
     SetConvArgs a{xk, sxk, xq, sxq, v, theta, Nk, Nq, C, p, unshared};
+    if (C <= kSmallC) {
+        dim3 grid((unsigned)ceil_div64(Nq, kSmallWarps), B);
+        switch (C) {
+            case 1: NPFK_LAUNCH(setconv_small_fwd_kernel<1>, grid, kSmallWarps * 32, 0, as_stream(stream), a, out, ldo); break;
+            case 2: NPFK_LAUNCH(setconv_small_fwd_kernel<2>, grid, kSmallWarps * 32, 0, as_stream(stream), a, out, ldo); break;
+            case 3: NPFK_LAUNCH(setconv_small_fwd_kernel<3>, grid, kSmallWarps * 32, 0, as_stream(stream), a, out, ldo); break;
+            default: NPFK_LAUNCH(setconv_small_fwd_kernel<4>, grid, kSmallWarps * 32, 0, as_stream(stream), a, out, ldo); break;
+        }
+        return check_launch("setconv_fwd");
+    }
     dim3 grid((unsigned)ceil_div64(Nq, kQT), B);
     NPFK_LAUNCH(setconv_fwd_kernel, grid, kSCThreads, 0, as_stream(stream), a, out, ldo);
     return check_launch("setconv_fwd");
@@ -311,9 +442,21 @@ int npfk_setconv_fwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq,
 int npfk_setconv_bwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq, const float* v, const float* theta,
                      const float* out, const float* dout, int64_t ldo, float* dv, float* dtheta, int B, int64_t Nk,
                      int64_t Nq, int C, float p, int unshared, void* stream) {
-    NPFK_REQUIRE(xk && xq && v && theta && out && dout && dv && dtheta, "setconv_bwd: null pointer");
+    NPFK_REQUIRE(xk && xq && v && theta && out && dout && dtheta, "setconv_bwd: null pointer");
     NPFK_REQUIRE(B > 0 && B <= 65535 && Nk > 0 && Nq > 0 && C > 0, "setconv_bwd: bad shape");
     NPFK_REQUIRE(ldo >= C + 1, "setconv_bwd: ldo=%lld < C+1", (long long)ldo);
+    SetConvArgs a{xk, sxk, xq, sxq, v, theta, Nk, Nq, C, p, unshared};
+    if (!dv && C <= kSmallC) {   // values are data (context -> grid): only the length scale has a gradient
+        dim3 grid((unsigned)ceil_div64(Nq, kSmallWarps), B);
+        switch (C) {
+            case 1: NPFK_LAUNCH(setconv_small_bwd_kernel<1>, grid, kSmallWarps * 32, 0, as_stream(stream), a, out, dout, ldo, dtheta); break;
+            case 2: NPFK_LAUNCH(setconv_small_bwd_kernel<2>, grid, kSmallWarps * 32, 0, as_stream(stream), a, out, dout, ldo, dtheta); break;
+            case 3: NPFK_LAUNCH(setconv_small_bwd_kernel<3>, grid, kSmallWarps * 32, 0, as_stream(stream), a, out, dout, ldo, dtheta); break;
+            default: NPFK_LAUNCH(setconv_small_bwd_kernel<4>, grid, kSmallWarps * 32, 0, as_stream(stream), a, out, dout, ldo, dtheta); break;
+        }
+        return check_launch("setconv_bwd");
+    }
+    NPFK_REQUIRE(dv, "setconv_bwd: dv may be null only for C <= %d", kSmallC);
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(setconv_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -324,7 +467,6 @@ int npfk_setconv_bwd(const float* xk, int64_t sxk, const float* xq, int64_t sxq,
         }
         attr_set = true;
     }
-    SetConvArgs a{xk, sxk, xq, sxq, v, theta, Nk, Nq, C, p, unshared};
     dim3 grid((unsigned)ceil_div64(Nq, kQT), B);
     NPFK_LAUNCH(setconv_bwd_kernel, grid, kSCThreads, sizeof(SCBwdSmem), as_stream(stream), a, out, dout, ldo, dv,
                 dtheta);

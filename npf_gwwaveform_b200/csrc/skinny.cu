@@ -34,10 +34,12 @@ __global__ void __launch_bounds__(256) skinny_expand_kernel(const ExpandArgs a) 
     for (int i = threadIdx.x; i < a.W; i += blockDim.x) sB[i] = a.bias ? __ldg(a.bias + i) : 0.f;
     __syncthreads();
     const int G = a.W >> 2;
+    const int gsh = (G & (G - 1)) == 0 ? 31 - __clz(G) : -1;
     const int64_t total = a.M * G;
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t m = e / G;
-        const int c = (int)(e % G) << 2;
+        // G is a power of two for every layer of the path (W = 32 / 128 / 256): shift and mask instead of a 64-bit divide
+        const int64_t m = gsh >= 0 ? (e >> gsh) : e / G;
+        const int c = (int)(gsh >= 0 ? (e & (G - 1)) : (e % G)) << 2;
         // products first, bias afterwards: the rounding order of addmm in the reference (matters for parity on
         // ill-conditioned gradients, e.g. the pretrained AttnCNP key transform)
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -304,7 +306,7 @@ int skinny_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ld
         return 0;
     }
     a.S = S;
-    int64_t ctas = ceil_div64(M, 2048);
+    int64_t ctas = ceil_div64(M, 64);         // at least 64 rows per CTA, at most four CTAs per SM
     if (ctas > (int64_t)kNumSMs * 4) ctas = (int64_t)kNumSMs * 4;
     a.rows_per_cta = ceil_div64(M, ctas);
     ctas = ceil_div64(M, a.rows_per_cta);

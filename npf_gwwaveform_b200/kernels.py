@@ -455,7 +455,8 @@ class _SetConvRbfFn(Function):
         xk, xq, v, theta, out = ctx.saved_tensors
         sxk, sxq, B, Nk, Nq, C, p, unshared = ctx.cfg
         dout = _c(dout)
-        dv = torch.zeros_like(v)
+        # values that are data (context -> grid) need no dv: few-channel inputs then take the length-scale-only kernel
+        dv = torch.zeros_like(v) if (ctx.needs_input_grad[2] or C > 4) else None
         dtheta = torch.zeros_like(theta)
         LIB.call("npfk_setconv_bwd", _p(xk), sxk, _p(xq), sxq, _p(v), _p(theta), _p(out), _p(dout), C + 1, _p(dv),
                  _p(dtheta), B, Nk, Nq, C, p, unshared, _st())

@@ -242,6 +242,38 @@ def test_setconv_interp_hoisted_resizer(B, Nk, Nq, C, O_, unshared, keys):
     check_grads(["dtheta"], [td.grad], [ts.grad], tol=2e-3)
 
 
+@pytest.mark.parametrize("B,Nk,Nq,C,unshared", [
+    (2, 512, 200, 1, False),    # C3's context -> grid shape
+    (3, 37, 70, 1, False), (2, 50, 9, 3, False), (2, 33, 40, 4, False), (2, 45, 33, 2, True), (1, 1, 3, 1, False),
+])
+def test_setconv_data_values(B, Nk, Nq, C, unshared):
+    """context -> grid: the values are data, so only the length scale (and the resizer) get gradients; few-channel
+    inputs take the warp-per-query kernels (forward for any C <= 4, backward when dv is not requested)."""
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    g = torch.Generator().manual_seed(Nk * 7 + Nq)
+    xk = torch.rand(B, Nk, 1, generator=g) * 2 - 1
+    xq = torch.linspace(-1.1, 1.1, Nq).view(1, Nq, 1).expand(B, Nq, 1)
+    v = torch.randn(B, Nk, C, generator=g)
+    sig = 3.0 / max(Nk, 8)
+    theta = torch.full((2 if unshared else 1,), math.log(math.expm1(sig)))
+    if unshared:
+        theta[1] += 0.3
+    W, bias = torch.randn(24, C + 1, generator=g) / math.sqrt(C + 1), torch.randn(24, generator=g)
+    dy = torch.randn(B, Nq, 24, generator=g)
+
+    ts, Ws, bs = cpu(theta, True), cpu(W, True), cpu(bias, True)
+    ref = _setconv_ref(xk.double(), xq.double(), v.double(), ts, Ws, bs, unshared)
+    ref.backward(dy.double())
+
+    td, Wd, bd = dev(theta, True), dev(W, True), dev(bias, True)
+    t = Kn.setconv_rbf(xk.cuda(), xq.cuda(), v.cuda(), td, 2.0, unshared)
+    out = Kn.linear(t, Wd, bd)
+    out.backward(dy.cuda())
+    assert rel_err(out, ref) < TOL
+    check_grads(["dtheta", "dW"], [td.grad, Wd.grad], [ts.grad, Ws.grad])
+
+
 def test_setconv_far_queries_are_defined():
     """G3: softmax weights stay defined when every exp underflows; density -> 0 (setcnn.py:134-140)"""
     from npf_gwwaveform_b200 import kernels as Kn
