@@ -29,9 +29,8 @@ def _norm_args(norm):
 
 def _norm_relu_dwconv(x, norm, conv, res, training, relu=True):
     gamma, beta, rm, rv, eps, mom = _norm_args(norm)
-    if gamma is not None and training:
-        norm.num_batches_tracked += 1
-    return K.norm_act_dwconv(x, gamma, beta, conv.weight, conv.bias, res, rm, rv, training, eps, mom, relu)
+    nbt = norm.num_batches_tracked if gamma is not None and training else None
+    return K.norm_act_dwconv(x, gamma, beta, conv.weight, conv.bias, res, rm, rv, training, eps, mom, relu, nbt)
 
 
 def _pointwise(x, conv):

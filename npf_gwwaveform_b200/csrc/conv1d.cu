@@ -32,9 +32,11 @@ bn_partial_kernel(const float* __restrict__ x, int64_t rows, int C, double* __re
 }
 
 __global__ void bn_finalize_kernel(const double* __restrict__ scratch, int64_t rows, int C, float* __restrict__ stats,
-                                   float* __restrict__ running_mean, float* __restrict__ running_var, float momentum) {
+                                   float* __restrict__ running_mean, float* __restrict__ running_var, float momentum,
+                                   long long* __restrict__ num_batches_tracked) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
+    if (c == 0 && num_batches_tracked) *num_batches_tracked += 1;
     const double n = (double)rows;
     const double mean = scratch[c] / n;
     double var = scratch[C + c] / n - mean * mean;
@@ -140,11 +142,7 @@ dwconv_fwd_win_kernel(const float* __restrict__ x, const NormArgs nrm, const flo
         if (l0 + l < L) {
             float acc = bv;
 #pragma unroll
-            for (int j = 0; j < KS; ++j) {
-                // out-of-range taps are skipped like in the generic kernel (keeps -0.0 / NaN behaviour identical)
-                const int li = l0 + l + j - PAD;
-                if (li >= 0 && li < L) acc = fmaf(wr[j], hw[l + j], acc);
-            }
+            for (int j = 0; j < KS; ++j) acc = fmaf(wr[j], hw[l + j], acc);   // hw is 0 outside [0, L): exact no-op
             if (res) acc += rs[l];
             yb[(int64_t)(l0 + l) * C] = acc;
         }
@@ -225,7 +223,7 @@ dwconv_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, con
 // B*L/LC (same-address atomics serialise in L2: that was most of the kernel's time).
 constexpr int kDwSlices = 8;
 template <int KS, int LC>
-__global__ void __launch_bounds__(32 * kDwSlices)
+__global__ void __launch_bounds__(32 * kDwSlices, 2)
 dwconv_bwd_win_kernel(const float* __restrict__ dy, const float* __restrict__ x, const NormArgs nrm,
                       const float* __restrict__ w, float* __restrict__ dh, float* __restrict__ dw,
                       float* __restrict__ dbias, float* __restrict__ sums, int B, int L, int C, int relu) {
@@ -422,7 +420,7 @@ using namespace npfk;
 extern "C" {
 
 int npfk_bn_stats(const float* x, int64_t rows, int C, double* scratch, float* stats, float* running_mean,
-                  float* running_var, float momentum, void* stream) {
+                  float* running_var, float momentum, int64_t* num_batches_tracked, void* stream) {
     NPFK_REQUIRE(x && scratch && stats, "bn_stats: null pointer");
     NPFK_REQUIRE(rows > 0 && C > 0, "bn_stats: bad shape");
     NPFK_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_stats: running stats must come in pairs");
@@ -438,7 +436,7 @@ int npfk_bn_stats(const float* x, int64_t rows, int C, double* scratch, float* s
     int rc = check_launch("bn_partial");
     if (rc != NPFK_OK) return rc;
     NPFK_LAUNCH(bn_finalize_kernel, (C + 127) / 128, 128, 0, st, scratch, rows, C, stats, running_mean, running_var,
-                momentum);
+                momentum, reinterpret_cast<long long*>(num_batches_tracked));
     return check_launch("bn_finalize");
 }
 
@@ -487,7 +485,7 @@ int npfk_dwconv_bwd(const float* dy, const float* x, const float* mean, const fl
     NPFK_REQUIRE(ks > 0 && ks % 2 == 1 && ks <= kDwMaxKs, "dwconv_bwd: kernel size %d must be odd and <= %d", ks, kDwMaxKs);
     NPFK_REQUIRE(!mean || (var && gamma && beta), "dwconv_bwd: incomplete normalisation arguments");
     NormArgs n{mean, var, gamma, beta, eps};
-    constexpr int kWinLC = 16;
+    constexpr int kWinLC = 8;
     dim3 wgrid((C + 31) / 32, (unsigned)ceil_div64((int64_t)((L + kWinLC - 1) / kWinLC) * B, kDwSlices));
 #define NPFK_DW_WIN(KS_)                                                                                              \
     case KS_:                                                                                                         \

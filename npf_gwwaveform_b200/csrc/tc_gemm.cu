@@ -125,6 +125,7 @@ struct NtParams {
     int relu, round_out;
     int side_mode;        // 0: none / generic loads, 1: residual via TMA (tmE), 2: mask via TMA (tmE)
     int num_stages, b_bytes;   // smem ring depth, bytes of the B operand per stage
+    int slice_n;          // output columns per CTA column slice (blockIdx.y): 256, or narrower when M alone cannot fill the SMs
     int* g_abort;
 };
 
@@ -167,7 +168,7 @@ __host__ __device__ inline uint32_t tmem_cols_for(int need) {
     return c;
 }
 
-// Y tile [128 x Nc] = A[128 x K] . B^T ; one CTA column slice of at most 256 columns (blockIdx.y)
+// Y tile [128 x Nc] = A[128 x K] . B^T ; one CTA column slice of at most p.slice_n <= 256 columns (blockIdx.y)
 template <bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -176,8 +177,8 @@ tc_gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int stage_bytes = kABytes + p.b_bytes;
     const SmemLayout sm = carve_smem(smem_raw, p.num_stages, stage_bytes, kEpiBytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n0 = blockIdx.y * 256;
-    const int Nc = min(256, p.N - n0);
+    const int n0 = blockIdx.y * p.slice_n;
+    const int Nc = min(p.slice_n, p.N - n0);
     const int Npad = (Nc + 31) & ~31;
     const uint32_t tmem_cols = tmem_cols_for(2 * Npad);
     const int64_t num_tiles = (p.M + kBlockM - 1) / kBlockM;
@@ -553,8 +554,13 @@ template <bool B_MN>
 static int launch_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int N,
                      int K, const float* bias, const float* res, int64_t ldres, int64_t res_rows, const float* mask,
                      int64_t ldmask, int relu, int round_out, cudaStream_t st) {
-    const int n_slices = (N + 255) / 256;
-    const int Nc_max = N < 256 ? N : 256;
+    // column slices of 256; when the row tiles alone leave SMs idle (the UNet's 6144-row pointwise convolutions),
+    // halve the slice while the finer split still fits one wave: more CTAs share the operand traffic and the epilogue
+    const int64_t tiles = (M + kBlockM - 1) / kBlockM;
+    int slice_n = 256;
+    while (slice_n > 32 && tiles * ((N + slice_n / 2 - 1) / (slice_n / 2)) <= kNumSMs) slice_n >>= 1;
+    const int n_slices = (N + slice_n - 1) / slice_n;
+    const int Nc_max = N < slice_n ? N : slice_n;
     const int Npad = (Nc_max + 31) & ~31;
     CUtensorMap tmA, tmB, tmC;
     int rc = encode_tmap_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kBlockM);
@@ -582,6 +588,7 @@ static int launch_nt(const float* A, int64_t lda, const float* B, int64_t ldb, f
     p.relu = relu; p.round_out = round_out;
     p.side_mode = side_mode;
     p.b_bytes = Npad * 128;
+    p.slice_n = slice_n;
     const int stage_bytes = kABytes + p.b_bytes;
     int stages = (kStageBytesMax - 4096 - kEpiBytes) / stage_bytes;
     if (stages > 8) stages = 8;
@@ -601,7 +608,6 @@ static int launch_nt(const float* A, int64_t lda, const float* B, int64_t ldb, f
         }
         attr_done[B_MN] = true;
     }
-    const int64_t tiles = (M + kBlockM - 1) / kBlockM;
     int gx = kNumSMs / n_slices;
     if (gx < 1) gx = 1;
     if (tiles < gx) gx = (int)tiles;

@@ -525,7 +525,7 @@ class _NormActDwConvFn(Function):
 
     @staticmethod
     def forward(ctx, x, gamma, beta, w, bias, res, running_mean, running_var, training: bool, eps: float,
-                momentum: float, relu: bool):
+                momentum: float, relu: bool, num_batches_tracked=None):
         require_cuda(x, w)
         x, w = _c(x), _c(w)
         B, L, C = x.shape
@@ -541,7 +541,7 @@ class _NormActDwConvFn(Function):
                 stats = torch.empty(2 * C, device=x.device, dtype=torch.float32)
                 scratch = torch.empty(2 * C, device=x.device, dtype=torch.float64)
                 LIB.call("npfk_bn_stats", _p(x), B * L, C, _p(scratch), _p(stats), _p(running_mean), _p(running_var),
-                         float(momentum), st)
+                         float(momentum), _p(num_batches_tracked), st)
                 mean, var = stats[:C], stats[C:]
             else:
                 mean, var = _c(running_mean), _c(running_var)
@@ -562,25 +562,28 @@ class _NormActDwConvFn(Function):
         st = _st()
         dev = x.device
         dh = torch.empty_like(x)
-        dw = torch.zeros(C, ks, device=dev, dtype=torch.float32)
-        dbias = torch.zeros(C, device=dev, dtype=torch.float32) if has_bias else None
-        sums = torch.zeros(2 * C, device=dev, dtype=torch.float32) if has_norm else None
+        # every "+=" output of the two kernels below comes out of one zero-filled buffer (one fill instead of five)
+        z = torch.zeros(C * (ks + 5), device=dev, dtype=torch.float32)
+        dw = z[:C * ks].view(C, ks)
+        dbias = z[C * ks:C * (ks + 1)] if has_bias else None
+        sums = z[C * (ks + 1):C * (ks + 3)] if has_norm else None
         LIB.call("npfk_dwconv_bwd", _p(dy), _p(x), _p(mean), _p(var), _p(gamma), _p(beta), eps, _p(w2), _p(dh), _p(dw),
                  _p(dbias), _p(sums), B, L, C, ks, int(relu), st)
         dgamma = dbeta = None
         dx = dh
         if has_norm:
-            dgamma = torch.zeros(C, device=dev, dtype=torch.float32)
-            dbeta = torch.zeros(C, device=dev, dtype=torch.float32)
+            dgamma, dbeta = z[C * (ks + 3):C * (ks + 4)], z[C * (ks + 4):]
             LIB.call("npfk_bn_bwd", _p(dh), _p(x), _p(mean), _p(var), _p(gamma), eps, _p(sums), _p(dx), _p(dgamma),
                      _p(dbeta), B * L, C, int(training), st)
         return (dx, dgamma, dbeta, dw.reshape(wshape), dbias, (dy if has_res else None), None, None, None, None, None,
-                None)
+                None, None)
 
 
-def norm_act_dwconv(x, gamma, beta, w, bias, res, running_mean, running_var, training, eps, momentum, relu=True):
+def norm_act_dwconv(x, gamma, beta, w, bias, res, running_mean, running_var, training, eps, momentum, relu=True,
+                    num_batches_tracked=None):
+    """``num_batches_tracked`` (BatchNorm1d's int64 buffer) is incremented on the device in training mode"""
     return _NormActDwConvFn.apply(x, gamma, beta, w, bias, res, running_mean, running_var, training, eps, momentum,
-                                  relu)
+                                  relu, num_batches_tracked)
 
 
 class _AvgPool2Fn(Function):

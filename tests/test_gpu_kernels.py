@@ -320,8 +320,10 @@ def test_norm_relu_dwconv(B, L, C, ks, norm, training, with_res):
     gd, btd = (dev(gam, True), dev(bet, True)) if norm else (None, None)
     rmd, rvd = (rm.cuda(), rv.cuda()) if norm else (None, None)
     rd = dev(res, True) if with_res else None
-    y = Kn.norm_act_dwconv(xd, gd, btd, wd, bd, rd, rmd, rvd, training, 1e-5, 0.1, True)
+    nbt = torch.tensor(3, device="cuda") if norm and training else None
+    y = Kn.norm_act_dwconv(xd, gd, btd, wd, bd, rd, rmd, rvd, training, 1e-5, 0.1, True, nbt)
     y.backward(dy.cuda())
+    assert nbt is None or int(nbt) == 4        # BatchNorm1d.num_batches_tracked += 1, on the device
     assert rel_err(y, ref) < TOL
     check_grads(["dx", "dw", "dbias"], [xd.grad, wd.grad, bd.grad], [xs.grad, sd["c.weight"].grad, sd["c.bias"].grad])
     if norm:
