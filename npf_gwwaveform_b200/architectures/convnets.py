@@ -34,7 +34,7 @@ def _norm_relu_dwconv(x, norm, conv, res, training, relu=True):
 
 
 def _pointwise(x, conv):
-    return K.linear(x, conv.weight[:, :, 0], conv.bias)
+    return K.linear(x, conv.weight, conv.bias)      # [N, K, 1] weight taken as is (no view node in the graph)
 
 
 class DepthSepConv1d(nn.Module):

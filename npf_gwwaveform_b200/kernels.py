@@ -58,6 +58,23 @@ def _c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     return t if t.is_contiguous() else t.contiguous()
 
 
+def set_direct_grad(flag: bool) -> None:
+    """Direct-gradient mode (FlatAdamTrainer.capture turns it on while recording): the "+=" weight-gradient kernels add
+    straight into ``param.grad`` (the trainer's zeroed flat buffer) and the autograd node returns None for that
+    parameter, instead of zero-filling a fresh buffer that autograd then adds to ``param.grad`` (two tiny kernels per
+    parameter per step).  No AccumulateGrad hook fires for such a parameter."""
+    _state["direct_grad"] = bool(flag)
+
+
+def _grad_sink(p, shape=None):
+    if not _state.get("direct_grad") or not isinstance(p, torch.nn.Parameter) or p.grad is None:
+        return None
+    g = p.grad
+    if g.dtype != torch.float32 or not g.is_contiguous() or not g.is_cuda:
+        return None
+    return g if shape is None else g.view(shape)
+
+
 def _rows_view(x: torch.Tensor):
     """(tensor, ld) such that x can be read as M rows of K elements with row stride ld (no copy when possible)."""
     K = x.shape[-1]
@@ -119,6 +136,10 @@ class _LinearFn(Function):
     @staticmethod
     def forward(ctx, x, w, b, res, relu: bool):
         require_cuda(x, w, b, res)
+        ctx.wb = (w, b)
+        ctx.w_shape = w.shape
+        if w.dim() == 3:          # pointwise Conv1d weight [N, K, 1]
+            w = w.reshape(w.shape[0], w.shape[1])
         N, K = w.shape
         lead = x.shape[:-1]
         xv, ldx = _rows_view(x)
@@ -167,9 +188,12 @@ class _LinearFn(Function):
         need_b = ctx.has_b and ctx.needs_input_grad[2]
         if ctx.needs_input_grad[0]:
             dx = torch.empty(*dy.shape[:-1], K, device=dy.device, dtype=torch.float32)
+        sink_w = _grad_sink(ctx.wb[0], (N, K)) if need_w else None
+        sink_b = _grad_sink(ctx.wb[1]) if need_b else None
         if need_w or need_b:
-            dw = torch.zeros(N, K, device=dy.device, dtype=torch.float32)
-            db = torch.zeros(N, device=dy.device, dtype=torch.float32) if need_b else None
+            dw = sink_w if sink_w is not None else torch.zeros(N, K, device=dy.device, dtype=torch.float32)
+            if need_b:
+                db = sink_b if sink_b is not None else torch.zeros(N, device=dy.device, dtype=torch.float32)
         if dx is not None and dw is not None and M > 0:
             LIB.call("npfk_linear_bwd_fused", _p(g), N, _p(xv), ldx, _p(wv), ldw, 0, _p(dx), K, _p(dw), K, _p(db),
                      M, N, K, ctx.mode, st)
@@ -184,7 +208,8 @@ class _LinearFn(Function):
             else:
                 dres = torch.empty(ctx.res_shape, device=dy.device, dtype=torch.float32)
                 LIB.call("npfk_rows_fold_sum", _p(g), N, _p(dres), N, res_rows, M // res_rows, N, st)
-        return dx, dw, db, dres, None
+        dw = None if (sink_w is not None or not need_w or dw is None) else dw.reshape(ctx.w_shape)
+        return dx, dw, (None if sink_b is not None else db), dres, None
 
 
 def linear(x, w, b=None, res=None, relu=False):
@@ -245,6 +270,7 @@ class _MlpChainFn(Function):
                 acts.append(y)
         ctx.cfg = (out_relu, x_is_relu, dy_premasked, mode, M, n_layers, dims, res is not None,
                    None if res is None else res.shape, [wb[2 * i + 1] is not None for i in range(n_layers)], x.shape)
+        ctx.wb = wb
         ctx.save_for_backward(h if (out_relu and not dy_premasked) else None, *acts, *wvs)
         return h.reshape(*lead, dims[-1][0])
 
@@ -277,9 +303,14 @@ class _MlpChainFn(Function):
             masked = i > 0 or x_is_relu
             dw = db = None
             if need_w:
-                dw = torch.zeros(N, Kd, device=g.device, dtype=torch.float32)
-                db = torch.zeros(N, device=g.device, dtype=torch.float32) if has_b[i] else None
-                grads_wb[2 * i], grads_wb[2 * i + 1] = dw, db
+                sink_w = _grad_sink(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[5 + 2 * i] else None
+                sink_b = _grad_sink(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[6 + 2 * i] else None
+                dw = sink_w if sink_w is not None else torch.zeros(N, Kd, device=g.device, dtype=torch.float32)
+                db = None
+                if has_b[i]:
+                    db = sink_b if sink_b is not None else torch.zeros(N, device=g.device, dtype=torch.float32)
+                grads_wb[2 * i] = None if sink_w is not None else dw
+                grads_wb[2 * i + 1] = None if sink_b is not None else db
             if need_w and need_dx and M > 0:
                 # one pass over g and the saved input: dgrad (+ ReLU mask from hin) and wgrad together
                 dx = torch.empty(M, Kd, device=g.device, dtype=torch.float32)
@@ -549,6 +580,7 @@ class _NormActDwConvFn(Function):
         y = torch.empty_like(x)
         LIB.call("npfk_dwconv_fwd", _p(x), _p(mean), _p(var), _p(gamma), _p(beta), float(eps), _p(w2), _p(bias_c),
                  _p(res_c), _p(y), B, L, C, ks, int(relu), st)
+        ctx.params = (gamma, beta, w, bias)
         ctx.save_for_backward(x, gamma, beta, w2, mean, var)
         ctx.cfg = (B, L, C, ks, has_norm, bool(training), float(eps), bool(relu), bias is not None, res is not None,
                    w.shape)
@@ -564,18 +596,27 @@ class _NormActDwConvFn(Function):
         dh = torch.empty_like(x)
         # every "+=" output of the two kernels below comes out of one zero-filled buffer (one fill instead of five)
         z = torch.zeros(C * (ks + 5), device=dev, dtype=torch.float32)
-        dw = z[:C * ks].view(C, ks)
-        dbias = z[C * ks:C * (ks + 1)] if has_bias else None
+        pg, pb, pw, pbias = ctx.params
+        ng = ctx.needs_input_grad
+        sinks = (_grad_sink(pg) if ng[1] else None, _grad_sink(pb) if ng[2] else None,
+                 _grad_sink(pw, (C, ks)) if ng[3] else None, _grad_sink(pbias) if ng[4] else None)
+        dw = sinks[2] if sinks[2] is not None else z[:C * ks].view(C, ks)
+        dbias = (sinks[3] if sinks[3] is not None else z[C * ks:C * (ks + 1)]) if has_bias else None
         sums = z[C * (ks + 1):C * (ks + 3)] if has_norm else None
         LIB.call("npfk_dwconv_bwd", _p(dy), _p(x), _p(mean), _p(var), _p(gamma), _p(beta), eps, _p(w2), _p(dh), _p(dw),
                  _p(dbias), _p(sums), B, L, C, ks, int(relu), st)
         dgamma = dbeta = None
         dx = dh
         if has_norm:
-            dgamma, dbeta = z[C * (ks + 3):C * (ks + 4)], z[C * (ks + 4):]
+            dgamma = sinks[0] if sinks[0] is not None else z[C * (ks + 3):C * (ks + 4)]
+            dbeta = sinks[1] if sinks[1] is not None else z[C * (ks + 4):]
             LIB.call("npfk_bn_bwd", _p(dh), _p(x), _p(mean), _p(var), _p(gamma), eps, _p(sums), _p(dx), _p(dgamma),
                      _p(dbeta), B * L, C, int(training), st)
-        return (dx, dgamma, dbeta, dw.reshape(wshape), dbias, (dy if has_res else None), None, None, None, None, None,
+        if has_norm:
+            dgamma, dbeta = (None if sinks[0] is not None else dgamma), (None if sinks[1] is not None else dbeta)
+        dw = None if sinks[2] is not None else dw.reshape(wshape)
+        dbias = None if sinks[3] is not None else dbias
+        return (dx, dgamma, dbeta, dw, dbias, (dy if has_res else None), None, None, None, None, None,
                 None, None)
 
 

@@ -15,6 +15,7 @@ With world_size == 1 the same code runs without any collective.  BatchNorm stati
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, List, Optional
 
 import torch
@@ -57,8 +58,11 @@ class FlatAdamTrainer:
     # ------------------------------------------------------------------ flat storage
     def _build_flat(self, order: List[int]) -> None:
         dev = self.params[0].device
-        total = sum(p.numel() for p in self.params)
-        flat_p = torch.empty(total, device=dev, dtype=torch.float32)
+        # every parameter starts on a 128-byte boundary: the tensor-core weight-gradient kernels need 16-byte aligned
+        # outputs to take gradients straight into this buffer (kernels.set_direct_grad); the padding stays zero
+        pad = lambda n: (n + 31) & ~31  # noqa: E731
+        total = sum(pad(p.numel()) for p in self.params)
+        flat_p = torch.zeros(total, device=dev, dtype=torch.float32)
         flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
         old_m = getattr(self, "exp_avg", None)
         self.offsets = {}
@@ -71,7 +75,7 @@ class FlatAdamTrainer:
                 p.data = flat_p[off:off + n].view_as(p)
                 p.grad = flat_g[off:off + n].view_as(p)
                 self.offsets[i] = (off, n)
-                off += n
+                off += pad(n)
         self.flat_param, self.flat_grad = flat_p, flat_g
         if old_m is None:
             self.exp_avg = torch.zeros_like(flat_p)
@@ -160,6 +164,8 @@ class FlatAdamTrainer:
         self._static = {k: v.clone() for k, v in batch.items()}
         self._capturing = True
         self._graph = torch.cuda.CUDAGraph()
+        # weight-gradient kernels add straight into the flat gradient buffer (NPFK_DIRECT_GRAD=0: through autograd)
+        K.set_direct_grad(os.environ.get("NPFK_DIRECT_GRAD", "1") != "0")
         try:
             with torch.cuda.graph(self._graph):
                 self.flat_grad.zero_()
@@ -169,6 +175,7 @@ class FlatAdamTrainer:
                 self._static_loss = loss.detach()
         finally:
             self._capturing = False
+            K.set_direct_grad(False)
         for p_idx, p in enumerate(self.params):
             o, n = self.offsets[p_idx]
             assert p.grad is not None and p.grad.data_ptr() == self.flat_grad.data_ptr() + 4 * o, \

@@ -1,0 +1,67 @@
+"""CUDA-graph training step (FlatAdamTrainer.capture / step_graphed) against the eager step of the same trainer.
+
+The captured step records forward + loss + backward with the weight-gradient kernels adding straight into the flat
+gradient buffer (kernels.set_direct_grad); the eager step goes through autograd's AccumulateGrad.  Both must land on
+the same losses, gradients, parameters and BatchNorm buffers (up to the order of float atomics)."""
+import copy
+
+import pytest
+import torch
+
+from util_models import build_product, chirp_batch
+
+pytestmark = pytest.mark.gpu
+
+
+LR = 1e-6      # Adam turns rounding noise on exactly-zero gradients (a bias in front of BatchNorm) into +-lr steps, so the
+               # two runs are kept on (almost) the same trajectory and the gradients themselves are compared
+
+
+def _run(model, batches, n_eager):
+    import npf_gwwaveform_b200 as npf
+    from npf_gwwaveform_b200.training import FlatAdamTrainer
+
+    tr = FlatAdamTrainer(model, npf.CNPFLoss().train(), lr=LR)
+    losses = []
+    for i, b in enumerate(batches):
+        if i == n_eager:
+            tr.capture(b)
+        if i >= n_eager:
+            losses.append(float(tr.step_graphed(b).clone()))
+        else:
+            losses.append(float(tr.step(b)))
+    torch.cuda.synchronize()
+    return losses, {n: p.grad.detach().double().clone() for n, p in model.named_parameters()}
+
+
+@pytest.mark.parametrize("name,R,mode", [("CNP", 32, "fp32"), ("ConvCNP", 32, "fp32"), ("ConvCNP_unet", 32, "fp32"),
+                                         ("AttnCNP", 32, "fp32"), ("ConvCNP", 128, "fast"), ("AttnCNP", 128, "fast")])
+def test_graphed_step_matches_eager(name, R, mode):
+    import npf_gwwaveform_b200 as npf
+
+    npf.set_mode(mode)
+    try:
+        torch.manual_seed(3)
+        m_eager = build_product(name, R).cuda().train()
+        m_graph = copy.deepcopy(m_eager)
+        batches = [{k: v.cuda() for k, v in chirp_batch(4, 24, 160, s).items()} for s in range(5)]
+        l_eager, g_eager = _run(m_eager, batches, n_eager=len(batches))
+        l_graph, g_graph = _run(m_graph, batches, n_eager=2)
+        tol = 2e-4 if mode == "fp32" else 1e-2      # tf32 operands: the suite's gradient tolerance in fast mode
+        for a, b in zip(l_eager, l_graph):
+            assert abs(a - b) <= tol * max(1.0, abs(a)), (l_eager, l_graph)
+        gmax = max(float(g.abs().max()) for g in g_eager.values())
+        assert gmax > 0
+        for k in g_eager:          # last step's gradients, relative to the largest gradient entry of the model
+            err = float((g_eager[k] - g_graph[k]).abs().max()) / gmax
+            assert err < tol, (k, err)
+        sd_e, sd_g = m_eager.state_dict(), m_graph.state_dict()
+        for k in sd_e:
+            a, b = sd_e[k].double(), sd_g[k].double()
+            if k.endswith("num_batches_tracked"):
+                assert int(a) == int(b) == len(batches), k
+                continue
+            err = float((a - b).abs().max() / (a.abs().max() + 1e-3))
+            assert err < tol, (k, err)
+    finally:
+        npf.set_mode("fp32")
