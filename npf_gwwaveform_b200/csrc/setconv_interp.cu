@@ -385,11 +385,18 @@ setconv_interp_bwd_kernel(const InterpArgs a, const float* __restrict__ stats, c
                 for (int i = 0; i < kIQ; ++i) r[i] = s.dT[threadIdx.x][i];
             }
             // dp[q][k] += sum_c dT[q][c] v[k][c]      (thread = (q, key-half))
-            for (int cc = 0; cc < ncc; ++cc) {
-                const float t = s.dT[cc][ql];
+            // four channels per step: one 16-byte broadcast load of v serves four FMAs (dT and V are zero beyond ncc)
+            for (int cc = 0; cc < ncc; cc += 4) {
+                const float t0 = s.dT[cc][ql], t1 = s.dT[cc + 1][ql], t2 = s.dT[cc + 2][ql], t3 = s.dT[cc + 3][ql];
 #pragma unroll
                 for (int i = 0; i < kIK / 2; ++i)
-                    if (half + 2 * i < nAct) dp[i] = fmaf(t, s.V[half + 2 * i][cc], dp[i]);
+                    if (half + 2 * i < nAct) {
+                        const float4 v4 = *reinterpret_cast<const float4*>(&s.V[half + 2 * i][cc]);
+                        dp[i] = fmaf(t0, v4.x, dp[i]);
+                        dp[i] = fmaf(t1, v4.y, dp[i]);
+                        dp[i] = fmaf(t2, v4.z, dp[i]);
+                        dp[i] = fmaf(t3, v4.w, dp[i]);
+                    }
             }
             // dv[k][c] += sum_q w[k][q] dT[q][c]        (thread = channel, dout row in registers)
             if ((int)threadIdx.x < ncc) {

@@ -11,6 +11,7 @@ ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import npf_gwwaveform_b200 as npf  # noqa: E402
+from npf_gwwaveform_b200 import kernels as Kn  # noqa: E402
 from npf_gwwaveform_b200.neuralproc import set_lazy_validation  # noqa: E402
 from npf_gwwaveform_b200.training import FlatAdamTrainer  # noqa: E402
 from util_models import build_product, chirp_batch  # noqa: E402
@@ -27,6 +28,7 @@ tr = FlatAdamTrainer(m, crit, lr=1e-3)
 for _ in range(3):
     tr.step(inp)
 torch.cuda.synchronize()
+Kn.set_direct_grad(os.environ.get("NPFK_DIRECT_GRAD", "0") == "1")
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True, record_shapes=True) as prof:
     tr.step(inp)
     torch.cuda.synchronize()
@@ -34,7 +36,7 @@ cnt = Counter()
 for ev in prof.events():
     if ev.device_type == torch.autograd.DeviceType.CPU and ev.name.startswith("aten::") and ev.cuda_time_total > 0 \
             and not any(c.cuda_time_total > 0 and c.name.startswith("aten::") for c in ev.cpu_children):
-        src = next((s for s in ev.stack if "/npf_gwwaveform_b200/" in s or "/tests/" in s), ev.stack[0] if ev.stack else "?")
+        src = next((s for s in ev.stack if "npf_gwwaveform_b200/" in s or "tests/" in s), ev.stack[0] if ev.stack else "?")
         cnt[(ev.name, str(ev.input_shapes)[:60], src.split("/root/repo/")[-1][:90])] += 1
 for (n, sh, src), c in cnt.most_common(60):
     print(f"{c:4d}  {n:28s} {sh:60s} {src}")
