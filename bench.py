@@ -144,7 +144,7 @@ def run_reference(args):
         "note": "reference = unmodified algorithm of MarinerQ/npf_GWwaveform restated in oracle/npf_oracle.py (the Python "
                 "reference itself cannot travel to the GPU box); runs on host cores only",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ clocks
@@ -389,7 +389,7 @@ def run_infer(args):
                         "std to host"},
         "gpu_launches": launches, "roofline": roofline,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -533,13 +533,29 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         rate, desc, cores, _ = cpu_reference_rate(args.workload, seconds=args.cpu_seconds)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def emit(line):
+    """the ONE JSON line, on the process's original stdout"""
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
     args = parse()
+    # Libraries print on stdout behind our back (NCCL's version banner under NCCL_DEBUG=VERSION is a plain printf):
+    # keep a private handle on the real stdout for the JSON line and point fd 1 at stderr for everything else.
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     elif args.workload.endswith("_infer"):
