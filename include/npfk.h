@@ -113,8 +113,10 @@ int npfk_mha_bwd(const float* q, const float* k, const float* v, const float* ou
  */
 int npfk_add_layernorm_fwd(const float* a, const float* b, const float* gamma, const float* beta, float* out,
                            float* mean, float* rstd, int64_t rows, int C, float eps, void* stream);
-/* ds = d(a+b) ; dgamma, dbeta are "+=" */
-int npfk_add_layernorm_bwd(const float* dout, const float* a, const float* b, const float* gamma,
+/* ds = d(a+b) ; dgamma, dbeta are "+=".  dout2 (may be NULL) is a second gradient of the output, added to dout while
+ * it is read: where the LayerNorm output feeds two consumers (c and MLP(c) in the transformer block) the fan-out sum
+ * costs one extra read here instead of a separate three-tensor add. */
+int npfk_add_layernorm_bwd(const float* dout, const float* dout2, const float* a, const float* b, const float* gamma,
                            const float* mean, const float* rstd, float* ds, float* dgamma, float* dbeta,
                            int64_t rows, int C, void* stream);
 

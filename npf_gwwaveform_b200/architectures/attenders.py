@@ -5,6 +5,7 @@ Mirrors the reference's attender registry and module layouts (npf/architectures/
 heads are read in place (no permute copies, no [B*H, Nq, Nk] logits in HBM).
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -12,6 +13,8 @@ import torch.nn as nn
 from .. import kernels as K
 from ..utils.initialization import weights_init
 from .blocks import MLP
+
+_USE_STASH = os.environ.get("NPFK_LN_STASH", "1") != "0"   # developer switch for A/B timing
 
 __all__ = ["get_attender", "DotAttender", "MultiheadAttender", "TransformerAttender"]
 
@@ -123,5 +126,8 @@ class TransformerAttender(MultiheadAttender):
     def forward(self, keys, queries, values, **kwargs):
         ctx = super().forward(keys, queries, values, **kwargs)
         ln1, ln2 = self.layer_norm1, self.layer_norm2
-        c = K.add_layernorm(ctx, queries, ln1.weight, ln1.bias, ln1.eps)   # residual on the raw queries
-        return K.add_layernorm(c, self.mlp(c), ln2.weight, ln2.bias, ln2.eps)
+        # c feeds LN2 directly and through the MLP: LN2's backward parks its gradient for c in `stash` and LN1's
+        # backward adds it to the MLP's while reading it (no separate fan-out add of two [B, Nt, 128] tensors)
+        stash = K.GradStash() if torch.is_grad_enabled() and _USE_STASH else None
+        c = K.add_layernorm(ctx, queries, ln1.weight, ln1.bias, ln1.eps, extra=stash)   # residual on the raw queries
+        return K.add_layernorm(c, self.mlp(c), ln2.weight, ln2.bias, ln2.eps, park_a=stash)

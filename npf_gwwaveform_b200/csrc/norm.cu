@@ -47,9 +47,10 @@ add_layernorm_fwd_kernel(const float* __restrict__ a, const float* __restrict__ 
     }
 }
 
-template <int PL>
+template <int PL, bool HAS2>
 __global__ void __launch_bounds__(256)
-add_layernorm_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ a, const float* __restrict__ b,
+add_layernorm_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ dout2, const float* __restrict__ a,
+                         const float* __restrict__ b,
                          const float* __restrict__ gamma, const float* __restrict__ mean,
                          const float* __restrict__ rstd, float* __restrict__ ds, float* __restrict__ dgamma,
                          float* __restrict__ dbeta, int64_t rows, int C) {
@@ -77,6 +78,7 @@ add_layernorm_bwd_kernel(const float* __restrict__ dout, const float* __restrict
                 t = a[row * C + c];
                 if (b) t += b[row * C + c];
                 g = dout[row * C + c];
+                if (HAS2) g += dout2[row * C + c];    // second gradient of the output (fan-out summed here, not by autograd)
                 t = (t - mu) * rs;
             }
             xh[i] = t;
@@ -301,7 +303,7 @@ int npfk_add_layernorm_fwd(const float* a, const float* b, const float* gamma, c
     return check_launch("add_layernorm_fwd");
 }
 
-int npfk_add_layernorm_bwd(const float* dout, const float* a, const float* b, const float* gamma, const float* mean,
+int npfk_add_layernorm_bwd(const float* dout, const float* dout2, const float* a, const float* b, const float* gamma, const float* mean,
                            const float* rstd, float* ds, float* dgamma, float* dbeta, int64_t rows, int C,
                            void* stream) {
     NPFK_REQUIRE(dout && a && gamma && mean && rstd && ds && dgamma && dbeta, "add_layernorm_bwd: null pointer");
@@ -309,9 +311,19 @@ int npfk_add_layernorm_bwd(const float* dout, const float* a, const float* b, co
     if (rows <= 0) return NPFK_OK;
     cudaStream_t st = as_stream(stream);
     const unsigned grid = (unsigned)min(ceil_div64(rows, 8 * 16), (int64_t)kNumSMs * 4);
-    if (C <= 128) NPFK_LAUNCH(add_layernorm_bwd_kernel<4>, grid, 256, 0, st, dout, a, b, gamma, mean, rstd, ds, dgamma, dbeta, rows, C);
-    else if (C <= 256) NPFK_LAUNCH(add_layernorm_bwd_kernel<8>, grid, 256, 0, st, dout, a, b, gamma, mean, rstd, ds, dgamma, dbeta, rows, C);
-    else NPFK_LAUNCH(add_layernorm_bwd_kernel<32>, grid, 256, 0, st, dout, a, b, gamma, mean, rstd, ds, dgamma, dbeta, rows, C);
+#define NPFK_LN_BWD(PL_, H2_)                                                                                        \
+    NPFK_LAUNCH((add_layernorm_bwd_kernel<PL_, H2_>), grid, 256, 0, st, dout, dout2, a, b, gamma, mean, rstd, ds,      \
+                dgamma, dbeta, rows, C)
+    if (dout2) {
+        if (C <= 128) NPFK_LN_BWD(4, true);
+        else if (C <= 256) NPFK_LN_BWD(8, true);
+        else NPFK_LN_BWD(32, true);
+    } else {
+        if (C <= 128) NPFK_LN_BWD(4, false);
+        else if (C <= 256) NPFK_LN_BWD(8, false);
+        else NPFK_LN_BWD(32, false);
+    }
+#undef NPFK_LN_BWD
     return check_launch("add_layernorm_bwd");
 }
 

@@ -428,10 +428,23 @@ def mha(q, k, v, n_heads: int, scale: float):
     return _MhaFn.apply(q, k, v, n_heads, scale)
 
 
+class GradStash:
+    """Side channel between two ``add_layernorm`` nodes of one transformer block, c = LN1(..) ; out = LN2(c + f(c)):
+    LN2's backward parks its gradient for the direct ``c`` input here instead of returning it, and LN1's backward adds
+    it to its incoming gradient inside the kernel (``dout2``).  autograd then never sums the two 537 MB gradients of
+    ``c`` with a separate kernel.  Valid because ``f(c)`` always back-propagates into ``c`` after LN2's backward ran."""
+
+    __slots__ = ("t",)
+
+    def __init__(self):
+        self.t = None
+
+
 class _AddLayerNormFn(Function):
     @staticmethod
-    def forward(ctx, a, b, gamma, beta, eps: float):
+    def forward(ctx, a, b, gamma, beta, eps: float, park_a: Optional[GradStash], extra: Optional[GradStash]):
         require_cuda(a, b, gamma, beta)
+        ctx.params = (gamma, beta)
         a, b, gamma, beta = _c(a), _c(b), _c(gamma), _c(beta)
         C = a.shape[-1]
         rows = a.numel() // C
@@ -442,6 +455,7 @@ class _AddLayerNormFn(Function):
                  float(eps), _st())
         ctx.save_for_backward(a, b, gamma, mean, rstd)
         ctx.has_b = b is not None
+        ctx.park_a, ctx.extra = park_a, extra
         return out
 
     @staticmethod
@@ -450,17 +464,29 @@ class _AddLayerNormFn(Function):
         C = a.shape[-1]
         rows = a.numel() // C
         dout = _c(dout)
+        dout2 = None
+        if ctx.extra is not None and ctx.extra.t is not None:
+            dout2, ctx.extra.t = ctx.extra.t, None
+            if dout2.shape != dout.shape:
+                raise NpfkError("add_layernorm: parked gradient does not match the incoming one")
         ds = torch.empty_like(a)
-        dg = torch.zeros_like(gamma)
-        db = torch.zeros_like(gamma)
-        LIB.call("npfk_add_layernorm_bwd", _p(dout), _p(a), _p(b), _p(gamma), _p(mean), _p(rstd), _p(ds), _p(dg), _p(db),
-                 rows, C, _st())
-        return ds, (ds if ctx.has_b else None), dg, db, None
+        pg, pb = ctx.params
+        sink_g = _grad_sink(pg) if ctx.needs_input_grad[2] else None
+        sink_b = _grad_sink(pb) if ctx.needs_input_grad[3] else None
+        dg = sink_g if sink_g is not None else torch.zeros_like(gamma)
+        db = sink_b if sink_b is not None else torch.zeros_like(gamma)
+        LIB.call("npfk_add_layernorm_bwd", _p(dout), _p(dout2), _p(a), _p(b), _p(gamma), _p(mean), _p(rstd), _p(ds),
+                 _p(dg), _p(db), rows, C, _st())
+        da = ds
+        if ctx.park_a is not None and ctx.has_b and ctx.needs_input_grad[0] and ctx.needs_input_grad[1]:
+            ctx.park_a.t, da = ds, None            # the producer of `a` picks it up as its dout2
+        return (da, (ds if ctx.has_b else None), (None if sink_g is not None else dg),
+                (None if sink_b is not None else db), None, None, None)
 
 
-def add_layernorm(a, b, gamma, beta, eps=1e-5):
-    """LayerNorm(a + b) over the last dim"""
-    return _AddLayerNormFn.apply(a, b, gamma, beta, eps)
+def add_layernorm(a, b, gamma, beta, eps=1e-5, park_a=None, extra=None):
+    """LayerNorm(a + b) over the last dim.  ``park_a`` / ``extra``: see GradStash (both ends must share one stash)."""
+    return _AddLayerNormFn.apply(a, b, gamma, beta, eps, park_a, extra)
 
 
 # ------------------------------------------------------------------------------------------ SetConv
@@ -888,8 +914,8 @@ class KernelTimer:
             rows, C = a[7], a[8]
             return 0.0, 4.0 * rows * C * (3 if a[1] else 2)
         if name == "npfk_add_layernorm_bwd":
-            rows, C = a[9], a[10]
-            return 0.0, 4.0 * rows * C * (4 if a[2] else 3)
+            rows, C = a[10], a[11]
+            return 0.0, 4.0 * rows * C * (3 + (1 if a[3] else 0) + (1 if a[1] else 0))
         if name == "npfk_gauss_nll_fwd":
             Z, B, T, yd = a[3:7]
             return 0.0, 4.0 * (Z * B * T * 2 * yd + B * T * yd)

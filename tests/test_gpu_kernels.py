@@ -156,6 +156,34 @@ def test_add_layernorm(rows, C, with_b):
         check_grads(["db"], [bd.grad], [bs.grad])
 
 
+def test_add_layernorm_parked_fanout_gradient():
+    """c = LN1(x + y); out = LN2(c + f(c)) with the GradStash side channel (LN2 parks its gradient for c, LN1 adds it
+    to f's while reading) against the same block through plain autograd fan-out."""
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    g = torch.Generator().manual_seed(11)
+    rows, C = 300, 128
+    x, y = torch.randn(rows, C, generator=g), torch.randn(rows, C, generator=g)
+    W = torch.randn(C, C, generator=g) / math.sqrt(C)
+    g1, b1, g2, b2 = (torch.randn(C, generator=g) * 0.3 + 1 for _ in range(4))
+    dy = torch.randn(rows, C, generator=g)
+
+    def block(use_stash):
+        ts = [dev(t, True) for t in (x, y, W, g1, b1, g2, b2)]
+        xd, yd, Wd, g1d, b1d, g2d, b2d = ts
+        st = Kn.GradStash() if use_stash else None
+        c = Kn.add_layernorm(xd, yd, g1d, b1d, extra=st)
+        out = Kn.add_layernorm(c, Kn.linear(c, Wd, relu=True), g2d, b2d, park_a=st)
+        out.backward(dy.cuda())
+        assert st is None or st.t is None          # consumed by LN1's backward
+        return out, [t.grad for t in ts]
+
+    o_ref, g_ref = block(False)
+    o_st, g_st = block(True)
+    assert torch.equal(o_ref, o_st)
+    check_grads(["dx", "dy", "dW", "dg1", "db1", "dg2", "db2"], g_st, [t.double().cpu() for t in g_ref], tol=1e-5)
+
+
 def _setconv_ref(xk, xq, v, theta, W, bias, unshared):
     sd = {"sc.radial_basis_func.length_scale_param": theta, "sc.resizer.weight": W, "sc.resizer.bias": bias}
     return O.set_conv(sd, "sc", xk, xq, v)
