@@ -60,7 +60,13 @@ int npfk_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx,
 /* dgrad + wgrad of one layer in one call: dx = (g . w) masked by (x > 0) when `masked`, dw += g^T . x,
  * db += sum_m g.  In NPFK_MODE_FAST with N == K == 128 this is ONE tcgen05 kernel that reads g and x from
  * HBM once (the ReLU mask is taken from x, the layer's saved input, which is also the wgrad operand);
- * every other shape/mode runs npfk_linear_bwd_dw followed by npfk_linear_bwd_dx. */
+ * every other shape/mode runs npfk_linear_bwd_dw followed by npfk_linear_bwd_dx.
+ * `masked` is a bit set: NPFK_BWD_MASKED (1) as above; NPFK_BWD_DX_ACCUMULATE (2): dx += instead of dx = (the dX
+ * tiles leave the kernel through a TMA reduce-add, so a gradient that already sits in dx -- the other branch of a
+ * fan-out -- is summed without a separate pass); only the fused tensor-core path supports it, every other
+ * shape/mode returns NPFK_ERR_UNSUPPORTED for that bit. */
+#define NPFK_BWD_MASKED 1
+#define NPFK_BWD_DX_ACCUMULATE 2
 int npfk_linear_bwd_fused(const float* g, int64_t ldg, const float* x, int64_t ldx, const float* w, int64_t ldw,
                           int masked, float* dx, int64_t lddx, float* dw, int64_t lddw, float* db, int64_t M, int N,
                           int K, int mode, void* stream);

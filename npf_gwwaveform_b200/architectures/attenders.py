@@ -102,9 +102,9 @@ class MultiheadAttender(nn.Module):
         std = math.sqrt(2.0 / (self.value_size + self.value_head_size))
         nn.init.normal_(self.value_transform.weight, mean=0, std=std)
 
-    def forward(self, keys, queries, values, **kwargs):
+    def forward(self, keys, queries, values, q_stash=None, **kwargs):
         k = K.linear(keys, self.key_transform.weight)
-        q = K.linear(queries, self.query_transform.weight, self.query_transform.bias)
+        q = K.linear(queries, self.query_transform.weight, self.query_transform.bias, dx_stash=q_stash)
         v = K.linear(values, self.value_transform.weight)
         ctx = self.dot.attend(k, q, v, n_heads=self.n_heads)
         if self.post_processor is not None:
@@ -124,10 +124,13 @@ class TransformerAttender(MultiheadAttender):
         self.reset_parameters()
 
     def forward(self, keys, queries, values, **kwargs):
-        ctx = super().forward(keys, queries, values, **kwargs)
+        # queries feed the query transform and LN1's residual: LN1's backward parks its gradient for them in `q_stash`
+        # and the query transform's backward adds its dx onto that buffer (TMA reduce-add in the fused kernel)
+        q_stash = K.GradStash() if torch.is_grad_enabled() and _USE_STASH else None
+        ctx = super().forward(keys, queries, values, q_stash=q_stash, **kwargs)
         ln1, ln2 = self.layer_norm1, self.layer_norm2
         # c feeds LN2 directly and through the MLP: LN2's backward parks its gradient for c in `stash` and LN1's
         # backward adds it to the MLP's while reading it (no separate fan-out add of two [B, Nt, 128] tensors)
         stash = K.GradStash() if torch.is_grad_enabled() and _USE_STASH else None
-        c = K.add_layernorm(ctx, queries, ln1.weight, ln1.bias, ln1.eps, extra=stash)   # residual on the raw queries
+        c = K.add_layernorm(ctx, queries, ln1.weight, ln1.bias, ln1.eps, extra=stash, park_b=q_stash)   # residual on the raw queries
         return K.add_layernorm(c, self.mlp(c), ln2.weight, ln2.bias, ln2.eps, park_a=stash)

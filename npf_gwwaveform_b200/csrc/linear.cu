@@ -385,6 +385,12 @@ int npfk_linear_bwd_fused(const float* g, int64_t ldg, const float* x, int64_t l
     if (M <= 0) return NPFK_OK;
     if (mode == NPFK_MODE_FAST && tc::fused_bwd_eligible(g, ldg, x, ldx, w, ldw, dx, lddx, dw, lddw, M, N, K))
         return tc::tc_linear_bwd_fused(g, ldg, x, ldx, w, ldw, masked, dx, lddx, dw, lddw, db, M, as_stream(stream));
+    if (masked & NPFK_BWD_DX_ACCUMULATE) {
+        set_error("linear_bwd_fused: dx accumulation needs the fused tensor-core kernel (fast mode, N = K = 128, M >= 128, "
+                  "16-byte aligned operands); got M=%lld N=%d K=%d mode=%d", (long long)M, N, K, mode);
+        return NPFK_ERR_UNSUPPORTED;
+    }
+    masked &= 1;
     int rc = npfk_linear_bwd_dw(g, ldg, x, ldx, dw, lddw, db, M, N, K, mode, stream);
     if (rc != NPFK_OK) return rc;
     return npfk_linear_bwd_dx(g, ldg, w, ldw, masked ? x : nullptr, masked ? ldx : 0, dx, lddx, M, N, K, mode, stream);

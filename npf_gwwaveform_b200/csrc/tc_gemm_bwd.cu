@@ -41,6 +41,7 @@ struct FusedBwdParams {
     float* dw; int64_t lddw;
     float* db;            // [128] "+=" or null
     int masked;           // dX is zeroed where H <= 0
+    int accumulate;       // dX tiles are added to the destination (TMA reduce) instead of stored
     int* g_abort;
 };
 
@@ -277,7 +278,8 @@ tc_linear_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmGk, const __gri
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0 && row0 < p.M) {
-                    tma_store_2d(&tmC, sb, cc * 32, (int)row0);
+                    if (p.accumulate) tma_reduce_add_2d(&tmC, sb, cc * 32, (int)row0);
+                    else tma_store_2d(&tmC, sb, cc * 32, (int)row0);
                     tma_store_commit();
                 }
             }
@@ -338,7 +340,8 @@ int tc_linear_bwd_fused(const float* g, int64_t ldg, const float* h, int64_t ldh
     FusedBwdParams p{};
     p.M = M;
     p.dw = dw; p.lddw = lddw; p.db = db;
-    p.masked = masked;
+    p.masked = masked & 1;
+    p.accumulate = (masked >> 1) & 1;
     p.g_abort = abort_flag_ptr();
     static bool attr_done = false;
     if (!attr_done) {

@@ -134,9 +134,10 @@ def tf32_weight(w: torch.Tensor) -> torch.Tensor:
 
 class _LinearFn(Function):
     @staticmethod
-    def forward(ctx, x, w, b, res, relu: bool):
+    def forward(ctx, x, w, b, res, relu: bool, dx_stash=None):
         require_cuda(x, w, b, res)
         ctx.wb = (w, b)
+        ctx.dx_stash = dx_stash
         ctx.w_shape = w.shape
         if w.dim() == 3:          # pointwise Conv1d weight [N, K, 1]
             w = w.reshape(w.shape[0], w.shape[1])
@@ -186,8 +187,19 @@ class _LinearFn(Function):
         dx = dw = db = dres = None
         need_w = ctx.needs_input_grad[1]
         need_b = ctx.has_b and ctx.needs_input_grad[2]
+        # another gradient of x parked by a later node of the forward graph (GradStash): the fused tensor-core kernel
+        # adds this layer's dx onto it (TMA reduce-add); other shapes / modes add it afterwards
+        parked, flags = None, 0
+        if ctx.dx_stash is not None and ctx.dx_stash.t is not None:
+            parked, ctx.dx_stash.t = ctx.dx_stash.t, None
         if ctx.needs_input_grad[0]:
-            dx = torch.empty(*dy.shape[:-1], K, device=dy.device, dtype=torch.float32)
+            fusable = (parked is not None and need_w and ctx.mode == MODE_FAST and N == 128 and K == 128 and M >= 128
+                       and parked.is_contiguous() and parked.numel() == M * K and parked.data_ptr() % 16 == 0
+                       and ldx % 4 == 0 and xv.data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0)
+            if fusable:
+                dx, flags, parked = parked.view(*dy.shape[:-1], K), 2, None
+            else:
+                dx = torch.empty(*dy.shape[:-1], K, device=dy.device, dtype=torch.float32)
         sink_w = _grad_sink(ctx.wb[0], (N, K)) if need_w else None
         sink_b = _grad_sink(ctx.wb[1]) if need_b else None
         if need_w or need_b:
@@ -195,7 +207,7 @@ class _LinearFn(Function):
             if need_b:
                 db = sink_b if sink_b is not None else torch.zeros(N, device=dy.device, dtype=torch.float32)
         if dx is not None and dw is not None and M > 0:
-            LIB.call("npfk_linear_bwd_fused", _p(g), N, _p(xv), ldx, _p(wv), ldw, 0, _p(dx), K, _p(dw), K, _p(db),
+            LIB.call("npfk_linear_bwd_fused", _p(g), N, _p(xv), ldx, _p(wv), ldw, flags, _p(dx), K, _p(dw), K, _p(db),
                      M, N, K, ctx.mode, st)
         elif M > 0:
             if dx is not None:
@@ -208,13 +220,16 @@ class _LinearFn(Function):
             else:
                 dres = torch.empty(ctx.res_shape, device=dy.device, dtype=torch.float32)
                 LIB.call("npfk_rows_fold_sum", _p(g), N, _p(dres), N, res_rows, M // res_rows, N, st)
+        if parked is not None and dx is not None:
+            dx = dx + parked.view_as(dx)
         dw = None if (sink_w is not None or not need_w or dw is None) else dw.reshape(ctx.w_shape)
-        return dx, dw, (None if sink_b is not None else db), dres, None
+        return dx, dw, (None if sink_b is not None else db), dres, None, None
 
 
-def linear(x, w, b=None, res=None, relu=False):
-    """act(x @ w.T + b + res); `res` rows are tiled over the rows of x when it has fewer rows."""
-    return _LinearFn.apply(x, w, b, res, relu)
+def linear(x, w, b=None, res=None, relu=False, dx_stash=None):
+    """act(x @ w.T + b + res); `res` rows are tiled over the rows of x when it has fewer rows.
+    ``dx_stash``: a GradStash whose parked tensor (another gradient of x) is added to this layer's dx."""
+    return _LinearFn.apply(x, w, b, res, relu, dx_stash)
 
 
 class _MlpChainFn(Function):
@@ -442,7 +457,8 @@ class GradStash:
 
 class _AddLayerNormFn(Function):
     @staticmethod
-    def forward(ctx, a, b, gamma, beta, eps: float, park_a: Optional[GradStash], extra: Optional[GradStash]):
+    def forward(ctx, a, b, gamma, beta, eps: float, park_a: Optional[GradStash], extra: Optional[GradStash],
+                park_b: Optional[GradStash]):
         require_cuda(a, b, gamma, beta)
         ctx.params = (gamma, beta)
         a, b, gamma, beta = _c(a), _c(b), _c(gamma), _c(beta)
@@ -455,7 +471,7 @@ class _AddLayerNormFn(Function):
                  float(eps), _st())
         ctx.save_for_backward(a, b, gamma, mean, rstd)
         ctx.has_b = b is not None
-        ctx.park_a, ctx.extra = park_a, extra
+        ctx.park_a, ctx.extra, ctx.park_b = park_a, extra, park_b
         return out
 
     @staticmethod
@@ -480,13 +496,19 @@ class _AddLayerNormFn(Function):
         da = ds
         if ctx.park_a is not None and ctx.has_b and ctx.needs_input_grad[0] and ctx.needs_input_grad[1]:
             ctx.park_a.t, da = ds, None            # the producer of `a` picks it up as its dout2
-        return (da, (ds if ctx.has_b else None), (None if sink_g is not None else dg),
-                (None if sink_b is not None else db), None, None, None)
+        dbr = ds if ctx.has_b else None
+        if ctx.park_b is not None and ctx.has_b and ctx.needs_input_grad[1]:
+            # b's other consumer (a Linear with dx_stash=park_b, back-propagated AFTER everything that reads `da`)
+            # adds its dx onto this buffer and returns the sum as b's only gradient
+            ctx.park_b.t, dbr = ds, None
+        return (da, dbr, (None if sink_g is not None else dg), (None if sink_b is not None else db), None, None, None,
+                None)
 
 
-def add_layernorm(a, b, gamma, beta, eps=1e-5, park_a=None, extra=None):
-    """LayerNorm(a + b) over the last dim.  ``park_a`` / ``extra``: see GradStash (both ends must share one stash)."""
-    return _AddLayerNormFn.apply(a, b, gamma, beta, eps, park_a, extra)
+def add_layernorm(a, b, gamma, beta, eps=1e-5, park_a=None, extra=None, park_b=None):
+    """LayerNorm(a + b) over the last dim.  ``park_a`` / ``extra`` / ``park_b``: see GradStash (the producing and the
+    consuming node must share one stash)."""
+    return _AddLayerNormFn.apply(a, b, gamma, beta, eps, park_a, extra, park_b)
 
 
 # ------------------------------------------------------------------------------------------ SetConv

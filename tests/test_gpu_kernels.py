@@ -184,6 +184,39 @@ def test_add_layernorm_parked_fanout_gradient():
     check_grads(["dx", "dy", "dW", "dg1", "db1", "dg2", "db2"], g_st, [t.double().cpu() for t in g_ref], tol=1e-5)
 
 
+@pytest.mark.parametrize("mode,rows", [("fp32", 300), ("fast", 300), ("fast", 148 * 128 + 50)])
+def test_linear_dx_onto_parked_gradient(mode, rows):
+    """q = Linear(x); c = LN(f(q) + x): LN parks its gradient for x and the Linear's backward adds its dx onto it
+    (TMA reduce-add in the fused tensor-core kernel in fast mode, a plain add otherwise) - against autograd's fan-out."""
+    import npf_gwwaveform_b200 as npf
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    g = torch.Generator().manual_seed(5)
+    C = 128
+    x = torch.randn(rows, C, generator=g)
+    Wq, bq = torch.randn(C, C, generator=g) / math.sqrt(C), torch.randn(C, generator=g) * 0.1
+    g1, b1 = torch.randn(C, generator=g) * 0.3 + 1, torch.randn(C, generator=g) * 0.1
+    dy = torch.randn(rows, C, generator=g)
+    npf.set_mode(mode)
+    try:
+        def block(use_stash):
+            xd, Wd, bd, g1d, b1d = (dev(t, True) for t in (x, Wq, bq, g1, b1))
+            st = Kn.GradStash() if use_stash else None
+            q = Kn.linear(xd, Wd, bd, dx_stash=st)
+            out = Kn.add_layernorm(torch.tanh(q), xd, g1d, b1d, park_b=st)
+            out.backward(dy.cuda())
+            assert st is None or st.t is None
+            return out, [xd.grad, Wd.grad, bd.grad, g1d.grad, b1d.grad]
+
+        o_ref, g_ref = block(False)
+        o_st, g_st = block(True)
+        assert torch.equal(o_ref, o_st)
+        check_grads(["dx", "dW", "db", "dg1", "db1"], g_st, [t.double().cpu() for t in g_ref],
+                    tol=1e-5 if mode == "fp32" else 1e-4)
+    finally:
+        npf.set_mode("fp32")
+
+
 def _setconv_ref(xk, xq, v, theta, W, bias, unshared):
     sd = {"sc.radial_basis_func.length_scale_param": theta, "sc.resizer.weight": W, "sc.resizer.bias": bias}
     return O.set_conv(sd, "sc", xk, xq, v)
