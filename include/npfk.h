@@ -107,11 +107,13 @@ int npfk_set_mean_bwd(const float* dout, float* dx, int B, int64_t N, int C, voi
 int npfk_mha_fwd(const float* q, const float* k, const float* v, float* out, float* lse, int B, int64_t Nq,
                  int64_t Nk, int H, int D, float scale, int mode, void* stream);
 /* dq,dk,dv have the layouts of q,k,v (overwritten).  delta_ws: caller workspace of npfk_mha_bwd_ws_floats(B,Nq,H)
- * floats, 16-byte aligned (sum_d dO*O and log2-domain lse, padded to whole query tiles). */
+ * floats, 16-byte aligned: [B,H,Nqp] log2-domain lse, then [B,H,Nqp] delta = sum_d dO*O, Nqp = Nq rounded up to 64.
+ * delta_ready != 0 (tensor-core path only): the delta half already holds the values of the real queries -- written by
+ * the kernel that produced dO (npfk_add_layernorm_bwd, attn_delta) -- so O and dO are not read a second time. */
 int64_t npfk_mha_bwd_ws_floats(int B, int64_t Nq, int H);
 int npfk_mha_bwd(const float* q, const float* k, const float* v, const float* out, const float* lse,
                  const float* dout, float* dq, float* dk, float* dv, float* delta_ws, int B, int64_t Nq, int64_t Nk,
-                 int H, int D, float scale, int mode, void* stream);
+                 int H, int D, float scale, int delta_ready, int mode, void* stream);
 
 /* ---- residual + LayerNorm ---------------------------------------------------------------------
  * LN(a + b) of TransformerAttender.forward (attention.py:583-588).  b may be NULL.
@@ -124,7 +126,10 @@ int npfk_add_layernorm_fwd(const float* a, const float* b, const float* gamma, c
  * costs one extra read here instead of a separate three-tensor add. */
 int npfk_add_layernorm_bwd(const float* dout, const float* dout2, const float* a, const float* b, const float* gamma,
                            const float* mean, const float* rstd, float* ds, float* dgamma, float* dbeta,
-                           int64_t rows, int C, void* stream);
+                           int64_t rows, int C, float* attn_delta, int H, int64_t Nq, int64_t Nqp, void* stream);
+/* attn_delta (may be NULL; needs C == 16*H <= 128, Nq % 8 == 0, 16-byte aligned): `a` is the output O of npfk_mha_fwd with H heads of 16 and
+ * rows = B*Nq, so ds is the dO of npfk_mha_bwd: attn_delta[(b*H + h)*Nqp + q] = sum_d ds[row, 16h+d] * a[row, 16h+d]
+ * is written while both are in registers (the delta half of npfk_mha_bwd's workspace, see delta_ready). */
 
 /* ---- SetConv with the exponential RBF ----------------------------------------------------------
  * Replaces SetConv.forward + ExpRBF.forward up to (not including) the resizer Linear

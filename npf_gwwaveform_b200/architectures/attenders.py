@@ -58,12 +58,12 @@ class DotAttender(nn.Module):
     def reset_parameters(self):
         weights_init(self)
 
-    def attend(self, keys, queries, values, n_heads=1):
+    def attend(self, keys, queries, values, n_heads=1, delta_stash=None):
         d = queries.shape[-1] // n_heads
         scale = 1.0 / math.sqrt(d) if self.is_scale else 1.0
         if values.shape[-1] != keys.shape[-1]:
             raise NotImplementedError("fused attention needs value_size == kq_size")
-        return K.mha(queries, keys, values, n_heads, scale)
+        return K.mha(queries, keys, values, n_heads, scale, delta_stash)
 
     def forward(self, keys, queries, values, **kwargs):
         ctx = self.attend(keys, queries, values)
@@ -102,11 +102,12 @@ class MultiheadAttender(nn.Module):
         std = math.sqrt(2.0 / (self.value_size + self.value_head_size))
         nn.init.normal_(self.value_transform.weight, mean=0, std=std)
 
-    def forward(self, keys, queries, values, q_stash=None, **kwargs):
+    def forward(self, keys, queries, values, q_stash=None, delta_stash=None, **kwargs):
         k = K.linear(keys, self.key_transform.weight)
         q = K.linear(queries, self.query_transform.weight, self.query_transform.bias, dx_stash=q_stash)
         v = K.linear(values, self.value_transform.weight)
-        ctx = self.dot.attend(k, q, v, n_heads=self.n_heads)
+        ctx = self.dot.attend(k, q, v, n_heads=self.n_heads,
+                              delta_stash=delta_stash if self.post_processor is None else None)
         if self.post_processor is not None:
             ctx = K.linear(ctx, self.post_processor.weight, self.post_processor.bias)
         return ctx
@@ -127,10 +128,13 @@ class TransformerAttender(MultiheadAttender):
         # queries feed the query transform and LN1's residual: LN1's backward parks its gradient for them in `q_stash`
         # and the query transform's backward adds its dx onto that buffer (TMA reduce-add in the fused kernel)
         q_stash = K.GradStash() if torch.is_grad_enabled() and _USE_STASH else None
-        ctx = super().forward(keys, queries, values, q_stash=q_stash, **kwargs)
+        # LN1's backward produces dO of the attention with O in registers: it also writes delta = sum_d dO*O
+        d_stash = K.GradStash() if torch.is_grad_enabled() and _USE_STASH else None
+        ctx = super().forward(keys, queries, values, q_stash=q_stash, delta_stash=d_stash, **kwargs)
         ln1, ln2 = self.layer_norm1, self.layer_norm2
         # c feeds LN2 directly and through the MLP: LN2's backward parks its gradient for c in `stash` and LN1's
         # backward adds it to the MLP's while reading it (no separate fan-out add of two [B, Nt, 128] tensors)
         stash = K.GradStash() if torch.is_grad_enabled() and _USE_STASH else None
-        c = K.add_layernorm(ctx, queries, ln1.weight, ln1.bias, ln1.eps, extra=stash, park_b=q_stash)   # residual on the raw queries
+        c = K.add_layernorm(ctx, queries, ln1.weight, ln1.bias, ln1.eps, extra=stash, park_b=q_stash,
+                            attn_of=d_stash)   # residual on the raw queries
         return K.add_layernorm(c, self.mlp(c), ln2.weight, ln2.bias, ln2.eps, park_a=stash)

@@ -267,7 +267,7 @@ int attn_fwd_tc(const float* q, const float* k, const float* v, float* out, floa
 int64_t attn_bwd_ws_floats(int B, int64_t Nq, int H);
 int attn_bwd_tc(const float* q, const float* k, const float* v, const float* out, const float* lse, const float* dout,
                 float* dq, float* dk, float* dv, float* ws, int B, int64_t Nq, int64_t Nk, int H, int D, float scale,
-                cudaStream_t st);
+                int delta_ready, cudaStream_t st);
 }  // namespace tc
 
 }  // namespace npfk
@@ -305,13 +305,17 @@ int64_t npfk_mha_bwd_ws_floats(int B, int64_t Nq, int H) { return tc::attn_bwd_w
 
 int npfk_mha_bwd(const float* q, const float* k, const float* v, const float* out, const float* lse, const float* dout,
                  float* dq, float* dk, float* dv, float* delta_ws, int B, int64_t Nq, int64_t Nk, int H, int D,
-                 float scale, int mode, void* stream) {
+                 float scale, int delta_ready, int mode, void* stream) {
     NPFK_REQUIRE(q && k && v && out && lse && dout && dq && dk && dv && delta_ws, "mha_bwd: null pointer");
     NPFK_REQUIRE(B > 0 && Nq > 0 && Nk > 0 && H > 0, "mha_bwd: bad shape");
     NPFK_REQUIRE(H <= 65535 && B <= 65535, "mha_bwd: H and B must be <= 65535");
     cudaStream_t st = as_stream(stream);
     if (mode == NPFK_MODE_FAST && tc::attn_tc_eligible(q, k, v, out, B, Nq, Nk, H, D))
-        return tc::attn_bwd_tc(q, k, v, out, lse, dout, dq, dk, dv, delta_ws, B, Nq, Nk, H, D, scale, st);
+        return tc::attn_bwd_tc(q, k, v, out, lse, dout, dq, dk, dv, delta_ws, B, Nq, Nk, H, D, scale, delta_ready, st);
+    if (delta_ready) {
+        set_error("mha_bwd: delta_ready is only understood by the tensor-core path (fast mode, D in {16,32})");
+        return NPFK_ERR_UNSUPPORTED;
+    }
     NPFK_ATTN_DISPATCH(launch_bwd, q, k, v, out, lse, dout, dq, dk, dv, delta_ws, B, Nq, Nk, H, scale, st)
 }
 

@@ -63,12 +63,20 @@ struct AttnBwdParams {
 // main kernel can fetch them with aligned 1-D bulk copies and padded queries get P = 0.
 __global__ void attn_bwd_prep_kernel(const float* __restrict__ out, const float* __restrict__ dout,
                                      const float* __restrict__ lse, float* __restrict__ ws, int B, int H, int D,
-                                     int64_t Nq, int64_t Nqp) {
+                                     int64_t Nq, int64_t Nqp, int delta_ready) {
     const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int bh = blockIdx.y;
     if (q >= Nqp) return;
     const int b = bh / H, h = bh % H;
     float delta = 0.f, l2 = INFINITY;
+    if (delta_ready) {
+        // delta of the real queries was written by the producer of dO (npfk_add_layernorm_bwd's attn_delta output):
+        // only the log2-domain lse and the zero padding are left to do, without reading O and dO again
+        if (q < Nq) l2 = __ldg(lse + (int64_t)bh * Nq + q) * 1.4426950408889634f;
+        ws[(int64_t)bh * Nqp + q] = l2;
+        if (q >= Nq) ws[((int64_t)B * H + bh) * Nqp + q] = 0.f;
+        return;
+    }
     if (q < Nq) {
         const int64_t off = ((int64_t)b * Nq + q) * (H * D) + h * D;
         const float4* o4 = reinterpret_cast<const float4*>(out + off);
@@ -414,7 +422,7 @@ int64_t attn_bwd_ws_floats(int B, int64_t Nq, int H) {
 
 int attn_bwd_tc(const float* q, const float* k, const float* v, const float* out, const float* lse, const float* dout,
                 float* dq, float* dk, float* dv, float* ws, int B, int64_t Nq, int64_t Nk, int H, int D, float scale,
-                cudaStream_t st) {
+                int delta_ready, cudaStream_t st) {
     const int E = H * D;
     if ((reinterpret_cast<uintptr_t>(ws) & 15) || (reinterpret_cast<uintptr_t>(dq) & 15) ||
         (reinterpret_cast<uintptr_t>(dk) & 15) || (reinterpret_cast<uintptr_t>(dv) & 15) ||
@@ -463,7 +471,7 @@ int attn_bwd_tc(const float* q, const float* k, const float* v, const float* out
     // prep: delta and lse*log2e into the padded workspace; dq (and dk/dv when the queries are split) are "+="
     {
         dim3 grid((unsigned)((p.Nqp + 255) / 256), (unsigned)(B * H));
-        attn_bwd_prep_kernel<<<grid, 256, 0, st>>>(out, dout, lse, ws, B, H, D, Nq, p.Nqp);
+        attn_bwd_prep_kernel<<<grid, 256, 0, st>>>(out, dout, lse, ws, B, H, D, Nq, p.Nqp, delta_ready);
         count_launch();
     }
     cudaMemsetAsync(dq, 0, sizeof(float) * (size_t)B * Nq * E, st);

@@ -47,13 +47,19 @@ add_layernorm_fwd_kernel(const float* __restrict__ a, const float* __restrict__ 
     }
 }
 
-template <int PL, bool HAS2>
+struct LnDeltaArgs {
+    float* delta;          // [B, H, Nqp] or null
+    int H;
+    int64_t Nq, Nqp;
+};
+
+template <int PL, bool HAS2, bool HASD>
 __global__ void __launch_bounds__(256)
 add_layernorm_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ dout2, const float* __restrict__ a,
                          const float* __restrict__ b,
                          const float* __restrict__ gamma, const float* __restrict__ mean,
                          const float* __restrict__ rstd, float* __restrict__ ds, float* __restrict__ dgamma,
-                         float* __restrict__ dbeta, int64_t rows, int C) {
+                         float* __restrict__ dbeta, int64_t rows, int C, const LnDeltaArgs da) {
     __shared__ float sg[8][33];
     __shared__ float sb[8][33];
     const int lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
@@ -66,15 +72,37 @@ add_layernorm_bwd_kernel(const float* __restrict__ dout, const float* __restrict
         const int c = lane + 32 * i;
         gm[i] = (c < C) ? gamma[c] : 0.f;
     }
+    // delta output: the CTA's 8 warps own 8 consecutive rows of one task (Nq % 8 == 0); their 8 x H sums go through
+    // shared memory so that each head's 8 values leave as one 32-byte store.  (d_b, d_q) = (task, query) of the
+    // CTA's first row, advanced without a 64-bit division per row.
+    __shared__ __align__(16) float sD[2][8][8];
+    int64_t d_b = 0, d_q = 0;
+    uint32_t d_it = 0;
+    if (HASD) {
+        d_b = (warp - wl) / da.Nq;
+        d_q = (warp - wl) - d_b * da.Nq;
+    }
     for (int64_t row = warp; row < rows; row += nwarps) {
         const float mu = mean[row], rs = rstd[row];
-        float xh[PL], dxh[PL];
+        float xh[PL], dxh[PL], av[HASD ? PL : 1];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int i = 0; i < PL; ++i) {
             const int c = lane + 32 * i;
             float t = 0.f, g = 0.f;
-            if (c < C) {
+            if (HASD) {
+                // unconditional loads from a clamped column + selects: keeps all loads of the row in flight together
+                // (with the extra live value the compiler otherwise turns `c < C` into branches between the chunks)
+                const bool ok = c < C;
+                const int64_t e = row * C + (ok ? c : 0);
+                const float ta = a[e];
+                const float tb = b ? b[e] : 0.f;
+                float gg = dout[e];
+                if (HAS2) gg += dout2[e];
+                av[i] = ok ? ta : 0.f;
+                t = ok ? (ta + tb - mu) * rs : 0.f;
+                g = ok ? gg : 0.f;
+            } else if (c < C) {
                 t = a[row * C + c];
                 if (b) t += b[row * C + c];
                 g = dout[row * C + c];
@@ -93,7 +121,33 @@ add_layernorm_bwd_kernel(const float* __restrict__ dout, const float* __restrict
 #pragma unroll
         for (int i = 0; i < PL; ++i) {
             const int c = lane + 32 * i;
-            if (c < C) ds[row * C + c] = rs * (dxh[i] - s1 - xh[i] * s2);
+            const float dsv = rs * (dxh[i] - s1 - xh[i] * s2);
+            if (c < C) ds[row * C + c] = dsv;
+            if (HASD) {
+                // heads of 16 columns: columns lane + 32 i of a half warp belong to head 2 i + lane / 16
+                float pr = (c < C) ? dsv * av[i] : 0.f;
+                pr += __shfl_xor_sync(0xffffffffu, pr, 8);
+                pr += __shfl_xor_sync(0xffffffffu, pr, 4);
+                pr += __shfl_xor_sync(0xffffffffu, pr, 2);
+                pr += __shfl_xor_sync(0xffffffffu, pr, 1);
+                const int h = 2 * i + (lane >> 4);
+                if ((lane & 15) == 0 && h < da.H) sD[d_it & 1][h][wl] = pr;
+            }
+        }
+        if (HASD) {
+            __syncthreads();          // same trip count in all 8 warps: rows % 8 == 0
+            if (wl == 0 && lane < da.H) {
+                const float4* src = reinterpret_cast<const float4*>(sD[d_it & 1][lane]);
+                float4* dst = reinterpret_cast<float4*>(da.delta + (d_b * da.H + lane) * da.Nqp + d_q);
+                dst[0] = src[0];
+                dst[1] = src[1];
+            }
+            ++d_it;
+            d_q += nwarps;
+            while (d_q >= da.Nq) {
+                d_q -= da.Nq;
+                ++d_b;
+            }
         }
     }
 #pragma unroll
@@ -303,25 +357,33 @@ int npfk_add_layernorm_fwd(const float* a, const float* b, const float* gamma, c
     return check_launch("add_layernorm_fwd");
 }
 
-int npfk_add_layernorm_bwd(const float* dout, const float* dout2, const float* a, const float* b, const float* gamma, const float* mean,
-                           const float* rstd, float* ds, float* dgamma, float* dbeta, int64_t rows, int C,
-                           void* stream) {
+int npfk_add_layernorm_bwd(const float* dout, const float* dout2, const float* a, const float* b, const float* gamma,
+                           const float* mean, const float* rstd, float* ds, float* dgamma, float* dbeta, int64_t rows,
+                           int C, float* attn_delta, int H, int64_t Nq, int64_t Nqp, void* stream) {
     NPFK_REQUIRE(dout && a && gamma && mean && rstd && ds && dgamma && dbeta, "add_layernorm_bwd: null pointer");
     NPFK_REQUIRE(C > 0 && C <= 1024, "add_layernorm_bwd: C=%d outside (0,1024]", C);
+    NPFK_REQUIRE(!attn_delta || (H > 0 && C == 16 * H && C <= 128 && Nq > 0 && Nq % 8 == 0 && Nqp >= Nq &&
+                                 Nqp % 8 == 0 && rows % Nq == 0 && (reinterpret_cast<uintptr_t>(attn_delta) & 15) == 0),
+                 "add_layernorm_bwd: attn_delta needs C == 16*H <= 128, Nq %% 8 == 0 and rows == B*Nq (C=%d H=%d "
+                 "rows=%lld Nq=%lld)", C, H, (long long)rows, (long long)Nq);
+    const LnDeltaArgs da{attn_delta, H, Nq, Nqp};
     if (rows <= 0) return NPFK_OK;
     cudaStream_t st = as_stream(stream);
     const unsigned grid = (unsigned)min(ceil_div64(rows, 8 * 16), (int64_t)kNumSMs * 4);
-#define NPFK_LN_BWD(PL_, H2_)                                                                                        \
-    NPFK_LAUNCH((add_layernorm_bwd_kernel<PL_, H2_>), grid, 256, 0, st, dout, dout2, a, b, gamma, mean, rstd, ds,      \
-                dgamma, dbeta, rows, C)
-    if (dout2) {
-        if (C <= 128) NPFK_LN_BWD(4, true);
-        else if (C <= 256) NPFK_LN_BWD(8, true);
-        else NPFK_LN_BWD(32, true);
+#define NPFK_LN_BWD(PL_, H2_, HD_)                                                                                   \
+    NPFK_LAUNCH((add_layernorm_bwd_kernel<PL_, H2_, HD_>), grid, 256, 0, st, dout, dout2, a, b, gamma, mean, rstd, ds, \
+                dgamma, dbeta, rows, C, da)
+    if (attn_delta) {          // C == 16 H <= 128 checked above
+        if (dout2) NPFK_LN_BWD(4, true, true);
+        else NPFK_LN_BWD(4, false, true);
+    } else if (dout2) {
+        if (C <= 128) NPFK_LN_BWD(4, true, false);
+        else if (C <= 256) NPFK_LN_BWD(8, true, false);
+        else NPFK_LN_BWD(32, true, false);
     } else {
-        if (C <= 128) NPFK_LN_BWD(4, false);
-        else if (C <= 256) NPFK_LN_BWD(8, false);
-        else NPFK_LN_BWD(32, false);
+        if (C <= 128) NPFK_LN_BWD(4, false, false);
+        else if (C <= 256) NPFK_LN_BWD(8, false, false);
+        else NPFK_LN_BWD(32, false, false);
     }
 #undef NPFK_LN_BWD
     return check_launch("add_layernorm_bwd");

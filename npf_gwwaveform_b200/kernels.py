@@ -412,8 +412,9 @@ def set_mean(x):
 # ------------------------------------------------------------------------------------------ attention
 class _MhaFn(Function):
     @staticmethod
-    def forward(ctx, q, k, v, n_heads: int, scale: float):
+    def forward(ctx, q, k, v, n_heads: int, scale: float, delta_stash=None):
         require_cuda(q, k, v)
+        ctx.delta_stash = delta_stash
         q, k, v = _c(q), _c(k), _c(v)
         B, Nq, E = q.shape
         Nk = k.shape[1]
@@ -424,6 +425,8 @@ class _MhaFn(Function):
         LIB.call("npfk_mha_fwd", _p(q), _p(k), _p(v), _p(out), _p(lse), B, Nq, Nk, n_heads, D, float(scale), mode, _st())
         ctx.save_for_backward(q, k, v, out, lse)
         ctx.cfg = (B, Nq, Nk, n_heads, D, float(scale), mode)
+        if delta_stash is not None:        # what the consumer of `out` needs to write delta = sum_d dO*O for us
+            delta_stash.spec = (B, Nq, n_heads, D, mode, out.data_ptr())
         return out
 
     @staticmethod
@@ -432,15 +435,24 @@ class _MhaFn(Function):
         B, Nq, Nk, H, D, scale, mode = ctx.cfg
         dout = _c(dout)
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
-        ws = torch.empty(int(LIB.load().npfk_mha_bwd_ws_floats(B, Nq, H)), device=q.device, dtype=torch.float32)
+        ws, ready = None, 0
+        st_ = ctx.delta_stash
+        if st_ is not None and st_.t is not None:
+            ws_, ptr = st_.t
+            st_.t = None
+            if ptr == dout.data_ptr():     # delta was computed from exactly this dO
+                ws, ready = ws_, 1
+        if ws is None:
+            ws = torch.empty(int(LIB.load().npfk_mha_bwd_ws_floats(B, Nq, H)), device=q.device, dtype=torch.float32)
         LIB.call("npfk_mha_bwd", _p(q), _p(k), _p(v), _p(out), _p(lse), _p(dout), _p(dq), _p(dk), _p(dv), _p(ws), B, Nq,
-                 Nk, H, D, scale, mode, _st())
-        return dq, dk, dv, None, None
+                 Nk, H, D, scale, ready, mode, _st())
+        return dq, dk, dv, None, None, None
 
 
-def mha(q, k, v, n_heads: int, scale: float):
-    """softmax(q k^T * scale) v per head; heads are slices of the feature dim (no permutes)."""
-    return _MhaFn.apply(q, k, v, n_heads, scale)
+def mha(q, k, v, n_heads: int, scale: float, delta_stash=None):
+    """softmax(q k^T * scale) v per head; heads are slices of the feature dim (no permutes).
+    ``delta_stash``: GradStash shared with the ``add_layernorm`` that consumes the output as its ``a`` (attn_of=...)."""
+    return _MhaFn.apply(q, k, v, n_heads, scale, delta_stash)
 
 
 class GradStash:
@@ -449,16 +461,17 @@ class GradStash:
     it to its incoming gradient inside the kernel (``dout2``).  autograd then never sums the two 537 MB gradients of
     ``c`` with a separate kernel.  Valid because ``f(c)`` always back-propagates into ``c`` after LN2's backward ran."""
 
-    __slots__ = ("t",)
+    __slots__ = ("t", "spec")
 
     def __init__(self):
         self.t = None
+        self.spec = None
 
 
 class _AddLayerNormFn(Function):
     @staticmethod
     def forward(ctx, a, b, gamma, beta, eps: float, park_a: Optional[GradStash], extra: Optional[GradStash],
-                park_b: Optional[GradStash]):
+                park_b: Optional[GradStash], attn_of: Optional[GradStash]):
         require_cuda(a, b, gamma, beta)
         ctx.params = (gamma, beta)
         a, b, gamma, beta = _c(a), _c(b), _c(gamma), _c(beta)
@@ -472,6 +485,9 @@ class _AddLayerNormFn(Function):
         ctx.save_for_backward(a, b, gamma, mean, rstd)
         ctx.has_b = b is not None
         ctx.park_a, ctx.extra, ctx.park_b = park_a, extra, park_b
+        # `a` is the untouched output of mha (same storage): the backward can write the attention backward's delta
+        ctx.attn_of = attn_of if (attn_of is not None and attn_of.spec is not None
+                                  and attn_of.spec[5] == a.data_ptr()) else None
         return out
 
     @staticmethod
@@ -491,8 +507,18 @@ class _AddLayerNormFn(Function):
         sink_b = _grad_sink(pb) if ctx.needs_input_grad[3] else None
         dg = sink_g if sink_g is not None else torch.zeros_like(gamma)
         db = sink_b if sink_b is not None else torch.zeros_like(gamma)
+        delta, H, Nq, Nqp = None, 0, 0, 0
+        if ctx.attn_of is not None:
+            aB, aNq, aH, aD, amode, _ = ctx.attn_of.spec
+            if (amode == MODE_FAST and aD == 16 and aH % 2 == 0 and aH * 16 == C and C <= 128 and rows == aB * aNq
+                    and aNq % 8 == 0):
+                n_ws = int(LIB.load().npfk_mha_bwd_ws_floats(aB, aNq, aH))
+                ws = torch.empty(n_ws, device=a.device, dtype=torch.float32)
+                H, Nq, Nqp = aH, aNq, n_ws // (2 * aB * aH)
+                delta = ws[n_ws // 2:]
+                ctx.attn_of.t = (ws, ds.data_ptr())
         LIB.call("npfk_add_layernorm_bwd", _p(dout), _p(dout2), _p(a), _p(b), _p(gamma), _p(mean), _p(rstd), _p(ds),
-                 _p(dg), _p(db), rows, C, _st())
+                 _p(dg), _p(db), rows, C, _p(delta), H, Nq, Nqp, _st())
         da = ds
         if ctx.park_a is not None and ctx.has_b and ctx.needs_input_grad[0] and ctx.needs_input_grad[1]:
             ctx.park_a.t, da = ds, None            # the producer of `a` picks it up as its dout2
@@ -502,13 +528,14 @@ class _AddLayerNormFn(Function):
             # adds its dx onto this buffer and returns the sum as b's only gradient
             ctx.park_b.t, dbr = ds, None
         return (da, dbr, (None if sink_g is not None else dg), (None if sink_b is not None else db), None, None, None,
-                None)
+                None, None)
 
 
-def add_layernorm(a, b, gamma, beta, eps=1e-5, park_a=None, extra=None, park_b=None):
+def add_layernorm(a, b, gamma, beta, eps=1e-5, park_a=None, extra=None, park_b=None, attn_of=None):
     """LayerNorm(a + b) over the last dim.  ``park_a`` / ``extra`` / ``park_b``: see GradStash (the producing and the
-    consuming node must share one stash)."""
-    return _AddLayerNormFn.apply(a, b, gamma, beta, eps, park_a, extra, park_b)
+    consuming node must share one stash).  ``attn_of``: the stash given to the ``mha`` call that produced ``a``; the
+    backward then also writes the attention backward's delta = sum_d dO*O while ds (= dO) and a (= O) are in registers."""
+    return _AddLayerNormFn.apply(a, b, gamma, beta, eps, park_a, extra, park_b, attn_of)
 
 
 # ------------------------------------------------------------------------------------------ SetConv

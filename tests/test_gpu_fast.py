@@ -161,3 +161,38 @@ def test_mha_fast(B, Nq, Nk, H, D):
             assert float(a.abs().max()) < 2e-2      # tf32 rounding of dO.V against the fp32 dO.O
             continue
         assert rel_err(a, r) < 5e-3, (n, rel_err(a, r))
+
+
+@pytest.mark.parametrize("B,Nq,Nk,mode", [(2, 100, 37, "fast"), (3, 256, 128, "fast"), (2, 200, 64, "fast"),
+                                         (5, 1192, 300, "fast"), (2, 100, 37, "fp32")])
+def test_transformer_block_gradient_side_channels(B, Nq, Nk, mode):
+    """TransformerAttender with its three GradStash side channels (LN2 -> LN1 dout2, LN1 -> query transform dX
+    reduce-add, LN1 -> attention backward delta) against the same module with plain autograd fan-out sums."""
+    import npf_gwwaveform_b200 as npf
+    from npf_gwwaveform_b200.architectures import attenders
+
+    g = torch.Generator().manual_seed(B * 1000 + Nq)
+    keys, queries, values = (torch.randn(B, n, 128, generator=g) for n in (Nk, Nq, Nk))
+    dy = torch.randn(B, Nq, 128, generator=g)
+    torch.manual_seed(1)
+    mod = attenders.TransformerAttender(128, 128, 128, n_heads=8).cuda()
+    npf.set_mode(mode)
+    old = attenders._USE_STASH
+    try:
+        res = []
+        for use in (False, True):
+            attenders._USE_STASH = use
+            ins = [t.detach().cuda().requires_grad_(True) for t in (keys, queries, values)]
+            for p_ in mod.parameters():
+                p_.grad = None
+            out = mod(*ins)
+            out.backward(dy.cuda())
+            res.append((out.detach(), [t.grad for t in ins] + [p_.grad.clone() for p_ in mod.parameters()]))
+        assert torch.equal(res[0][0], res[1][0])
+        names = ["dkeys", "dqueries", "dvalues"] + [n for n, _ in mod.named_parameters()]
+        for n, a, b in zip(names, res[1][1], res[0][1]):
+            err = float((a - b).abs().max() / (b.abs().max() + 1e-12))
+            assert err < (5e-4 if mode == "fast" else 2e-5), (n, err)     # fast: tf32 operands re-truncate dS
+    finally:
+        attenders._USE_STASH = old
+        npf.set_mode("fp32")
