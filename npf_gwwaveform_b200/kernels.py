@@ -109,6 +109,12 @@ def _tf32_evict(base_id):
         _tf32_cache.pop(k, None)
 
 
+def tf32_cache_clear() -> None:
+    """Forget every rounded weight copy.  Needed after weights were changed behind autograd's back (a kernel writing
+    through raw pointers does not bump ``Tensor._version``): ``adam_step`` and ``FlatAdamTrainer`` call it."""
+    _tf32_cache.clear()
+
+
 def tf32_weight(w: torch.Tensor) -> torch.Tensor:
     """Round-to-nearest tf32 copy of a weight (tcgen05.mma.kind::tf32 truncates its fp32 operands).
 
@@ -921,6 +927,7 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step, gra
     require_cuda(param, grad, exp_avg, exp_avg_sq)
     LIB.call("npfk_adam_step", _p(param), _p(grad), _p(exp_avg), _p(exp_avg_sq), param.numel(), float(lr), float(beta1),
              float(beta2), float(eps), int(step), float(grad_scale), _st())
+    tf32_cache_clear()          # the parameters living in `param` changed without a version bump
 
 
 def launch_count() -> int:

@@ -139,6 +139,7 @@ class FlatAdamTrainer:
         self.step_count += 1
         self.adam_impl(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0],
                        self.betas[1], self.eps, self.step_count, 1.0 / self.world)
+        K.tf32_cache_clear()      # a custom adam_impl changes the weights without bumping tensor versions either
         if self._order is None:                           # calibration: re-lay the buffers in readiness order
             seen, order = set(), []
             for i in self._fired:
@@ -207,6 +208,7 @@ class FlatAdamTrainer:
         self.step_count += 1
         self.adam_impl(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0],
                        self.betas[1], self.eps, self.step_count, 1.0 / self.world)
+        K.tf32_cache_clear()      # a custom adam_impl changes the weights without bumping tensor versions either
         return self._static_loss
 
     def _gather_state(self, flat):

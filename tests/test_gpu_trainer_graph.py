@@ -65,3 +65,26 @@ def test_graphed_step_matches_eager(name, R, mode):
             assert err < tol, (k, err)
     finally:
         npf.set_mode("fp32")
+
+
+def test_eager_fast_steps_see_updated_weights():
+    """fast mode keeps rounded (tf32) copies of the weights; Adam updates the flat buffer through raw pointers, so the
+    copies must be dropped after every step: the trained module's forward has to match a fresh copy of itself."""
+    import npf_gwwaveform_b200 as npf
+    from npf_gwwaveform_b200.training import FlatAdamTrainer
+
+    npf.set_mode("fast")
+    try:
+        torch.manual_seed(5)
+        m = build_product("CNP", 128).cuda().train()
+        batches = [{k: v.cuda() for k, v in chirp_batch(4, 24, 160, s).items()} for s in range(4)]
+        tr = FlatAdamTrainer(m, npf.CNPFLoss().train(), lr=5e-2)      # big steps: stale copies would be far off
+        for b in batches[:3]:
+            tr.step(b)
+        m.eval()
+        with torch.no_grad():
+            ours = m(**batches[3])[0].mean.clone()
+            fresh = copy.deepcopy(m)(**batches[3])[0].mean
+        assert float((ours - fresh).abs().max()) <= 1e-6 * max(1.0, float(fresh.abs().max()))
+    finally:
+        npf.set_mode("fp32")
