@@ -115,11 +115,30 @@ def tf32_cache_clear() -> None:
     _tf32_cache.clear()
 
 
+def set_tf32_flat(src: Optional[torch.Tensor]) -> None:
+    """``src`` = a flat fp32 buffer holding many weights (FlatAdamTrainer.flat_param): rounds ALL of it with one
+    kernel, here, and until ``set_tf32_flat(None)`` ``tf32_weight`` hands out views of that one copy for every
+    contiguous weight living inside ``src``.  Used while a training step is captured into a CUDA graph: one rounding
+    launch per replay instead of one per weight."""
+    if src is None:
+        _state["tf32_flat"] = None
+        return
+    require_cuda(src)
+    out = torch.empty_like(src)
+    LIB.call("npfk_round_tf32", _p(src), _p(out), src.numel(), _st())
+    _state["tf32_flat"] = (src.data_ptr(), src.numel(), out)
+
+
 def tf32_weight(w: torch.Tensor) -> torch.Tensor:
     """Round-to-nearest tf32 copy of a weight (tcgen05.mma.kind::tf32 truncates its fp32 operands).
 
     Cached per parameter object (weak reference; views are keyed on their base) and parameter version, outside
     CUDA-graph capture; inside a capture the rounding kernel is always recorded so replays see current weights."""
+    flat = _state.get("tf32_flat")
+    if flat is not None and w.dtype == torch.float32 and w.is_contiguous():
+        off = w.data_ptr() - flat[0]
+        if off >= 0 and off % 4 == 0 and off // 4 + w.numel() <= flat[1]:
+            return flat[2][off // 4:off // 4 + w.numel()].view(w.shape)
     base = w._base if w._base is not None else w
     wv, _ = _weight_view(w.detach())
     if not wv.is_contiguous():

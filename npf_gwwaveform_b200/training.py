@@ -170,6 +170,8 @@ class FlatAdamTrainer:
         try:
             with torch.cuda.graph(self._graph):
                 self.flat_grad.zero_()
+                if K.get_mode() == K.MODE_FAST:       # one rounding kernel for every weight of the step
+                    K.set_tf32_flat(self.flat_param)
                 out = self.model(**self._static)
                 loss = self.criterion(out, self._static["Y_trgt"])
                 loss.backward()
@@ -177,6 +179,7 @@ class FlatAdamTrainer:
         finally:
             self._capturing = False
             K.set_direct_grad(False)
+            K.set_tf32_flat(None)
         for p_idx, p in enumerate(self.params):
             o, n = self.offsets[p_idx]
             assert p.grad is not None and p.grad.data_ptr() == self.flat_grad.data_ptr() + 4 * o, \
