@@ -190,6 +190,24 @@ class FlatAdamTrainer:
             self._flag_host = torch.zeros(1, dtype=self._flag_dev.dtype).pin_memory()
             self._flag_event = None
 
+    def prefetch(self, batch: dict) -> None:
+        """Start the H2D copy of the NEXT step's batch (pinned host tensors) on a side stream into a device staging
+        set, so that it overlaps the step running now; ``step_graphed(batch)`` with the same dict object then only
+        does a device-to-device copy into the graph's static inputs.  One batch can be in flight."""
+        if getattr(self, "_stage", None) is None:
+            self._stage = {k: torch.empty_like(v) for k, v in self._static.items()}
+            self._copy_stream = torch.cuda.Stream()
+            self._stage_ready = torch.cuda.Event()
+            self._stage_free = torch.cuda.Event()
+            self._stage_free.record()
+            self._stage_src = None
+        self._copy_stream.wait_event(self._stage_free)        # the previous staged batch has been consumed
+        with torch.cuda.stream(self._copy_stream):
+            for k, v in batch.items():
+                self._stage[k].copy_(v, non_blocking=True)
+            self._stage_ready.record()
+        self._stage_src = batch
+
     def step_graphed(self, batch: dict) -> torch.Tensor:
         """One optimisation step replaying the captured graph: H2D/D2D copy of the batch into the static buffers,
         graph replay, gradient all-reduce, Adam.  The [-1,1] range check of the reference (base.py:241-247) is
@@ -198,9 +216,16 @@ class FlatAdamTrainer:
             self._flag_event = None
             if int(self._flag_host.item()):
                 raise ValueError("Features during training should be in [-1,1] (detected on an earlier step).")
-        for k, v in batch.items():
-            if v is not self._static[k]:
-                self._static[k].copy_(v, non_blocking=True)
+        if getattr(self, "_stage_src", None) is batch:            # prefetched: wait for its H2D, then D2D
+            torch.cuda.current_stream().wait_event(self._stage_ready)
+            for k in batch:
+                self._static[k].copy_(self._stage[k], non_blocking=True)
+            self._stage_free.record()
+            self._stage_src = None
+        else:
+            for k, v in batch.items():
+                if v is not self._static[k]:
+                    self._static[k].copy_(v, non_blocking=True)
         self._graph.replay()
         if self._flag_dev is not None and self._flag_event is None:
             self._flag_host.copy_(self._flag_dev, non_blocking=True)
