@@ -136,7 +136,8 @@ def test_mha(B, Nq, Nk, H, D):
     check_grads(["dq", "dk", "dv"], [qd.grad, kd.grad, vd.grad], [qs.grad, ks.grad, vs.grad])
 
 
-@pytest.mark.parametrize("rows,C,with_b", [(33, 128, True), (7, 32, True), (1000, 256, False), (5, 1000, True)])
+@pytest.mark.parametrize("rows,C,with_b", [(33, 128, True), (7, 32, True), (1000, 256, False), (5, 1000, True),
+                                           (20001, 128, False), (1, 128, True)])
 def test_add_layernorm(rows, C, with_b):
     from npf_gwwaveform_b200 import kernels as Kn
 
