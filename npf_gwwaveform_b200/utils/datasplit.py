@@ -27,11 +27,12 @@ __all__ = ["get_all_indcs", "GetRangeIndcs", "GetIndcsMerger", "GetRandomIndcs",
 
 
 def _ratio_to_int(percentage, max_val):
-    """npf/utils/helpers.py ratio_to_int: a value in [0, 1] is a fraction of ``max_val``, anything else a count."""
-    if 0 <= percentage <= 1:
-        out = percentage * max_val
-    elif 1 <= percentage <= max_val:
+    """npf/utils/helpers.py:99-108 ratio_to_int: a value in [1, max_val] is a count (1 is ONE point, as in the
+    reference, which tests the count range first), a value in [0, 1) a fraction of ``max_val``."""
+    if 1 <= percentage <= max_val:
         out = percentage
+    elif 0 <= percentage < 1:
+        out = percentage * max_val
     else:
         raise ValueError(f"percentage={percentage} outside of [0,{max_val}].")
     return int(out)

@@ -129,3 +129,18 @@ def test_datasplit_host_rules():
         CntxtTrgtGetter()(torch.zeros(2, 5, 1), torch.zeros(2, 5, 1))
     with pytest.raises(NpfkError):
         g(2, 10, device="cpu")
+
+
+def test_ratio_to_int_matches_reference_order():
+    """npf/utils/helpers.py:99-108: [1, max] is a count (1 means ONE point), [0, 1) a fraction"""
+    from npf_gwwaveform_b200.utils.datasplit import _ratio_to_int
+
+    assert _ratio_to_int(1, 128) == 1
+    assert _ratio_to_int(50, 128) == 50
+    assert _ratio_to_int(0.5, 128) == 64
+    assert _ratio_to_int(0, 128) == 0
+    assert _ratio_to_int(0.999, 1000) == 999
+    with pytest.raises(ValueError):
+        _ratio_to_int(129, 128)
+    with pytest.raises(ValueError):
+        _ratio_to_int(-0.1, 128)
