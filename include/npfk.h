@@ -248,6 +248,11 @@ int npfk_range_flag(const float* x, int64_t n, float lo, float hi, int* flag, vo
  * step_count is the 1-based step index. grad_scale multiplies the gradient first (e.g. 1/world_size). */
 int npfk_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                    float beta1, float beta2, float eps, int step_count, float grad_scale, void* stream);
+/* The same with the step index kept in device memory: *step_count_dev is incremented first (one-thread kernel), then
+ * used as the 1-based step index.  Nothing in the launch depends on host state, so the optimiser step can be recorded
+ * into a CUDA graph together with forward, backward and the gradient all-reduce (training.FlatAdamTrainer.capture). */
+int npfk_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                       float beta1, float beta2, float eps, int* step_count_dev, float grad_scale, void* stream);
 
 #ifdef __cplusplus
 }

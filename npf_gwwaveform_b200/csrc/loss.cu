@@ -197,6 +197,27 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
     }
 }
 
+// Adam with the step number kept on the device (CUDA-graph friendly: nothing in the launch depends on the host's
+// step counter).  adam_step_inc_kernel advances the counter, adam_dev_kernel reads it and derives the bias corrections.
+__global__ void adam_step_inc_kernel(int* step) { *step += 1; }
+
+__global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                                int64_t n, float lr, float b1, float b2, float eps, const int* __restrict__ step,
+                                float grad_scale) {
+    const float t = (float)__ldg(step);
+    const float bc1 = 1.f - powf(b1, t);
+    const float bc2_sqrt = sqrtf(1.f - powf(b2, t));
+    const float step_size = lr / bc1;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float gi = g[i] * grad_scale;
+        const float mi = b1 * m[i] + (1.f - b1) * gi;
+        const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        p[i] -= step_size * mi / (sqrtf(vi) / bc2_sqrt + eps);
+    }
+}
+
 }  // namespace npfk
 
 using namespace npfk;
@@ -299,6 +320,16 @@ int npfk_adam_step(float* param, const float* grad, float* exp_avg, float* exp_a
     NPFK_LAUNCH(adam_kernel, ew_grid3(n), 256, 0, as_stream(stream), param, grad, exp_avg, exp_avg_sq, n, lr, beta1,
                 beta2, eps, bc1, bc2_sqrt, grad_scale);
     return check_launch("adam_step");
+}
+
+int npfk_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                       float beta2, float eps, int* step_count_dev, float grad_scale, void* stream) {
+    NPFK_REQUIRE(param && grad && exp_avg && exp_avg_sq && step_count_dev, "adam_step_dev: bad arguments");
+    NPFK_LAUNCH(adam_step_inc_kernel, 1, 1, 0, as_stream(stream), step_count_dev);
+    if (n <= 0) return check_launch("adam_step_dev");
+    NPFK_LAUNCH(adam_dev_kernel, ew_grid3(n), 256, 0, as_stream(stream), param, grad, exp_avg, exp_avg_sq, n, lr, beta1,
+                beta2, eps, step_count_dev, grad_scale);
+    return check_launch("adam_step_dev");
 }
 
 }  // extern "C"

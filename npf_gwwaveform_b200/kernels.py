@@ -66,7 +66,21 @@ def set_direct_grad(flag: bool) -> None:
     _state["direct_grad"] = bool(flag)
 
 
+def set_sink_callback(cb) -> None:
+    """``cb(param)`` is called each time a backward node is about to add a gradient straight into ``param.grad``
+    (direct-gradient mode); the kernel doing so is launched before the next such call.  FlatAdamTrainer uses it to
+    know when a gradient bucket is complete while the step is being captured."""
+    _state["sink_cb"] = cb
+
+
 def _grad_sink(p, shape=None):
+    g = _grad_sink_buf(p, shape)
+    if g is not None and _state.get("sink_cb") is not None:
+        _state["sink_cb"](p)
+    return g
+
+
+def _grad_sink_buf(p, shape=None):
     if not _state.get("direct_grad") or not isinstance(p, torch.nn.Parameter) or p.grad is None:
         return None
     g = p.grad
@@ -947,6 +961,16 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step, gra
     LIB.call("npfk_adam_step", _p(param), _p(grad), _p(exp_avg), _p(exp_avg_sq), param.numel(), float(lr), float(beta1),
              float(beta2), float(eps), int(step), float(grad_scale), _st())
     tf32_cache_clear()          # the parameters living in `param` changed without a version bump
+
+
+def adam_step_dev(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step_dev, grad_scale=1.0) -> None:
+    """``adam_step`` with the step index in device memory (int32 tensor, incremented by the call): capturable"""
+    require_cuda(param, grad, exp_avg, exp_avg_sq, step_dev)
+    assert step_dev.dtype == torch.int32 and step_dev.numel() == 1
+    LIB.call("npfk_adam_step_dev", _p(param), _p(grad), _p(exp_avg), _p(exp_avg_sq), param.numel(), float(lr),
+             float(beta1), float(beta2), float(eps), _p(step_dev), float(grad_scale), _st())
+    if not torch.cuda.is_current_stream_capturing():
+        tf32_cache_clear()
 
 
 def launch_count() -> int:

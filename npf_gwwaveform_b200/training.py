@@ -8,7 +8,9 @@ gradient all-reduce.  Design:
   in which backward finishes them (measured on a calibration step);
 * the flat gradient is cut into a few buckets; a bucket's NCCL all-reduce is issued from the
   post-accumulate-grad hook of its last parameter, so it travels over NVLink while backward is still running;
-* Adam runs as one npfk kernel over the flat buffers after the last bucket has landed.
+* Adam runs as one npfk kernel over the flat buffers after the last bucket has landed;
+* ``capture`` records the whole step - forward, loss, backward, the per-bucket all-reduces (forked onto NCCL's stream
+  in the middle of backward) and Adam (step index on the device) - into ONE CUDA graph; ``step_graphed`` replays it.
 
 With world_size == 1 the same code runs without any collective.  BatchNorm statistics stay per replica
 (SURVEY.md 8e default).
@@ -104,6 +106,9 @@ class FlatAdamTrainer:
     def _make_hook(self, i: int):
         def hook(_param):
             self._fired.append(i)
+            if getattr(self, "_event_cb", None) is not None:      # rehearsal / capture: the trainer decides what to launch
+                self._event_cb(i)
+                return
             if (self.overlap and self._order is not None and not getattr(self, "_capturing", False)
                     and self.bucket_last.get(self.bucket_of[i]) == i):
                 self._launch_bucket(self.bucket_of[i])
@@ -140,6 +145,8 @@ class FlatAdamTrainer:
         self.adam_impl(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0],
                        self.betas[1], self.eps, self.step_count, 1.0 / self.world)
         K.tf32_cache_clear()      # a custom adam_impl changes the weights without bumping tensor versions either
+        if getattr(self, "_step_dev", None) is not None:  # keep the captured graphs' step counter in sync
+            self._step_dev.fill_(self.step_count)
         if self._order is None:                           # calibration: re-lay the buffers in readiness order
             seen, order = set(), []
             for i in self._fired:
@@ -155,18 +162,73 @@ class FlatAdamTrainer:
         return loss.detach()
 
     # ------------------------------------------------------------------ CUDA-graph step
-    def capture(self, batch: dict) -> None:
-        """Record forward + loss + backward of one step into a CUDA graph (static copies of ``batch``'s tensors;
-        every later batch must have the same shapes).  Call after at least two eager ``step`` calls (buffers laid
-        out, kernels' one-time host initialisation done).  The gradient all-reduce and Adam stay outside the graph:
-        Adam's bias correction takes the step number as a host scalar."""
+    def _rehearse(self) -> None:
+        """One eager forward + backward in direct-gradient mode on the static batch that only records, in order, every
+        moment a parameter's gradient is (about to be) written: ``K._grad_sink`` calls of the "+=" weight-gradient
+        kernels and the post-accumulate hooks of everything else.  ``_bucket_ready[b]`` = index of the last such event
+        of bucket b's parameters: while capturing, bucket b's all-reduce is recorded as soon as a later event arrives
+        (the kernel behind a sink call is launched before the next call), so it forks off the main stream in the
+        middle of backward."""
+        index = {id(p): i for i, p in enumerate(self.params)}
+        seq: List[int] = []
+        self._event_cb = lambda i: seq.append(i)
+        K.set_sink_callback(lambda p: seq.append(index[id(p)]) if id(p) in index else None)
+        K.set_direct_grad(os.environ.get("NPFK_DIRECT_GRAD", "1") != "0")
+        try:
+            self.flat_grad.zero_()
+            out = self.model(**self._static)
+            self.criterion(out, self._static["Y_trgt"]).backward()
+        finally:
+            K.set_direct_grad(False)
+            K.set_sink_callback(None)
+            self._event_cb = None
+        self.flat_grad.zero_()
+        self._n_events = len(seq)
+        last = {}
+        for n, i in enumerate(seq):
+            last[i] = n
+        self._bucket_ready = []
+        for b in range(len(self.bucket_slices)):
+            members = [i for i in range(len(self.params)) if self.bucket_of[i] == b]
+            # a parameter that produced no event (no gradient this step) never blocks its bucket
+            self._bucket_ready.append(max([last[i] for i in members if i in last], default=-1))
+
+    def _capture_event(self, _i=None) -> None:
+        """called at every gradient event while capturing: record the all-reduce of every bucket that is complete"""
+        n = self._event_no
+        self._event_no += 1
+        while self._next_bucket < len(self.bucket_slices) and self._bucket_ready[self._next_bucket] < n:
+            self._launch_bucket(self._next_bucket)
+            self._next_bucket += 1
+
+    def capture(self, batch: dict, optimizer_in_graph: bool = True) -> None:
+        """Record one WHOLE optimisation step into a CUDA graph: zero the flat gradient, forward, loss, backward, the
+        gradient all-reduce (world > 1: one NCCL all-reduce per bucket, forked onto NCCL's stream as soon as the
+        bucket's last weight-gradient kernel has been recorded, joined before Adam) and the Adam update (step index
+        kept on the device, ``npfk_adam_step_dev``).  Static copies of ``batch``'s tensors are made; every later batch
+        must have the same shapes.  Call after at least two eager ``step`` calls (buffers laid out in readiness order,
+        kernels' one-time host initialisation done).  ``optimizer_in_graph=False`` keeps the round-1 behaviour (one
+        blocking all-reduce and an eager Adam launch after every replay)."""
         assert self._order is not None, "run eager steps before capture()"
         torch.cuda.synchronize()
         self._static = {k: v.clone() for k, v in batch.items()}
+        self._opt_in_graph = bool(optimizer_in_graph) and self.adam_impl is K.adam_step
+        if getattr(self, "_step_dev", None) is None:      # ONE device-side step counter shared by every captured graph
+            self._step_dev = torch.zeros(1, dtype=torch.int32, device=self.flat_param.device)
+        self._step_dev.fill_(self.step_count)
+        if self._opt_in_graph and self.world > 1:
+            self._rehearse()
+            torch.cuda.synchronize()
         self._capturing = True
         self._graph = torch.cuda.CUDAGraph()
         # weight-gradient kernels add straight into the flat gradient buffer (NPFK_DIRECT_GRAD=0: through autograd)
         K.set_direct_grad(os.environ.get("NPFK_DIRECT_GRAD", "1") != "0")
+        self._pending.clear()
+        self._event_no, self._next_bucket = 0, 0
+        fork = self._opt_in_graph and self.world > 1
+        if fork:
+            self._event_cb = self._capture_event
+            K.set_sink_callback(self._capture_event)
         try:
             with torch.cuda.graph(self._graph):
                 self.flat_grad.zero_()
@@ -176,9 +238,22 @@ class FlatAdamTrainer:
                 loss = self.criterion(out, self._static["Y_trgt"])
                 loss.backward()
                 self._static_loss = loss.detach()
+                if self._opt_in_graph:
+                    if fork:
+                        assert self._event_no == self._n_events, "the captured step differs from its rehearsal"
+                        while self._next_bucket < len(self.bucket_slices):
+                            self._launch_bucket(self._next_bucket)
+                            self._next_bucket += 1
+                        for w in self._pending:
+                            w.wait()
+                    K.adam_step_dev(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr,
+                                    self.betas[0], self.betas[1], self.eps, self._step_dev, 1.0 / self.world)
         finally:
             self._capturing = False
+            self._event_cb = None
+            self._pending.clear()
             K.set_direct_grad(False)
+            K.set_sink_callback(None)
             K.set_tf32_flat(None)
         for p_idx, p in enumerate(self.params):
             o, n = self.offsets[p_idx]
@@ -209,8 +284,9 @@ class FlatAdamTrainer:
         self._stage_src = batch
 
     def step_graphed(self, batch: dict) -> torch.Tensor:
-        """One optimisation step replaying the captured graph: H2D/D2D copy of the batch into the static buffers,
-        graph replay, gradient all-reduce, Adam.  The [-1,1] range check of the reference (base.py:241-247) is
+        """One optimisation step replaying the captured graph (forward, loss, backward, bucketed all-reduce, Adam) after
+        the H2D/D2D copy of the batch into the static buffers.  Returns the graph's static loss tensor: it is
+        OVERWRITTEN by the next replay, so read or clone it before the next call.  The [-1,1] range check of the reference (base.py:241-247) is
         read back asynchronously and raised at most one step late."""
         if self._flag_dev is not None and self._flag_event is not None and self._flag_event.query():
             self._flag_event = None
@@ -231,12 +307,13 @@ class FlatAdamTrainer:
             self._flag_host.copy_(self._flag_dev, non_blocking=True)
             self._flag_event = torch.cuda.Event()
             self._flag_event.record()
-        if self.world > 1:
-            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
         self.step_count += 1
-        self.adam_impl(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0],
-                       self.betas[1], self.eps, self.step_count, 1.0 / self.world)
-        K.tf32_cache_clear()      # a custom adam_impl changes the weights without bumping tensor versions either
+        if not self._opt_in_graph:
+            if self.world > 1:
+                dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+            self.adam_impl(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0],
+                           self.betas[1], self.eps, self.step_count, 1.0 / self.world)
+        K.tf32_cache_clear()      # the weights changed without bumping tensor versions
         return self._static_loss
 
     def _gather_state(self, flat):

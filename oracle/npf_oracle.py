@@ -209,7 +209,7 @@ def depthwise_conv(sd: SD, prefix: str, x: Tensor) -> Tensor:
     C, _, k = w.shape
     pad = k // 2
     B, L, _ = x.shape
-    xp = torch.zeros(B, L + 2 * pad, C, dtype=x.dtype)
+    xp = torch.zeros(B, L + 2 * pad, C, dtype=x.dtype, device=x.device)
     xp[:, pad:pad + L] = x
     y = torch.zeros_like(x)
     for j in range(k):
@@ -271,7 +271,7 @@ def upsample_linear2(x: Tensor) -> Tensor:
     Lo = 2 * L
     if L == 1:
         return x.expand(-1, Lo, -1).clone()
-    pos = torch.arange(Lo, dtype=x.dtype) * ((L - 1) / (Lo - 1))
+    pos = torch.arange(Lo, dtype=x.dtype, device=x.device) * ((L - 1) / (Lo - 1))
     i0 = pos.floor().long().clamp(max=L - 1)
     i1 = (i0 + 1).clamp(max=L - 1)
     lam = (pos - i0.to(x.dtype)).view(1, Lo, 1)
@@ -408,7 +408,7 @@ def cnp_forward(sd: SD, x_c: Tensor, y_c: Tensor, x_t: Tensor, training: bool = 
     B, Nc, _ = xc.shape
     r_dim = sd["decoder.resizer.to_hidden.weight"].shape[1]
     if Nc == 0:
-        R = torch.zeros(B, 1, r_dim, dtype=xt.dtype)
+        R = torch.zeros(B, 1, r_dim, dtype=xt.dtype, device=xt.device)
     else:
         R = merge_sum(sd, "xy_encoder", xc, y_c).mean(dim=1, keepdim=True)
     r_trgt = R.expand(B, xt.shape[1], r_dim).unsqueeze(0)
@@ -430,7 +430,8 @@ def _attn_det_path(sd, xc, y_c, xt, attention, n_heads):
     B, Nc, _ = xc.shape
     r_dim = sd["decoder.resizer.to_hidden.weight"].shape[1]
     if Nc == 0:
-        return torch.zeros(B, 0, r_dim, dtype=xt.dtype), torch.zeros(B, xt.shape[1], r_dim, dtype=xt.dtype)
+        return (torch.zeros(B, 0, r_dim, dtype=xt.dtype, device=xt.device),
+                torch.zeros(B, xt.shape[1], r_dim, dtype=xt.dtype, device=xt.device))
     R = merge_sum(sd, "xy_encoder", xc, y_c)
     if attention == "transformer":
         r_trgt = transformer_attender(sd, "attender", xc, xt, R, n_heads)
@@ -451,11 +452,11 @@ def convcnp_forward(sd: SD, x_c: Tensor, y_c: Tensor, x_t: Tensor, training: boo
     _check_range(training, x_c, x_t)
     B, Nc, _ = x_c.shape
     if x_induced is None:
-        x_induced = torch.linspace(-1.5, 1.5, int(density_induced * 3))
+        x_induced = torch.linspace(-1.5, 1.5, int(density_induced * 3), device=x_c.device)
     grid = x_induced.to(x_c.dtype).view(1, -1, 1).expand(B, -1, 1)
     r_dim = sd["cntxt_to_induced.resizer.weight"].shape[0]
     if Nc == 0:
-        R = torch.zeros(B, grid.shape[1], r_dim, dtype=x_c.dtype)
+        R = torch.zeros(B, grid.shape[1], r_dim, dtype=x_c.dtype, device=x_c.device)
     else:
         R = set_conv(sd, "cntxt_to_induced", x_c, grid, y_c)
     R = (unet_cnn if unet else cnn)(sd, "induced_to_induced", R, training, new_stats)
@@ -489,7 +490,7 @@ def lnp_forward(sd: SD, x_c: Tensor, y_c: Tensor, x_t: Tensor, y_t: Optional[Ten
 
     def enc(xe, y):
         if xe.shape[1] == 0:
-            return torch.zeros(B, 1, r_dim, dtype=xt.dtype)
+            return torch.zeros(B, 1, r_dim, dtype=xt.dtype, device=xt.device)
         return merge_sum(sd, "xy_encoder", xe, y).mean(dim=1, keepdim=True)
 
     R = enc(xc, y_c)
@@ -514,7 +515,7 @@ def attnlnp_forward(sd: SD, x_c: Tensor, y_c: Tensor, x_t: Tensor, y_t: Optional
 
     def pool(Rm):   # rep_to_lat_input (attnnp.py:172-181)
         if Rm.shape[1] == 0:
-            Rm = torch.zeros(B, 1, r_dim, dtype=xt.dtype)
+            Rm = torch.zeros(B, 1, r_dim, dtype=xt.dtype, device=xt.device)
         return Rm.mean(dim=1, keepdim=True)
 
     out: dict = {}
@@ -536,14 +537,14 @@ def convlnp_forward(sd: SD, x_c: Tensor, y_c: Tensor, x_t: Tensor, y_t: Optional
     global latent (neuralproc/helpers.py:21-34), SetConv on the n_z*B batch, decoder = DiscardIthArg(nn.Linear)."""
     _check_range(training, x_c, x_t)
     B, Nc, _ = x_c.shape
-    grid1 = torch.linspace(-1.5, 1.5, int(density_induced * 3)).to(x_c.dtype)
+    grid1 = torch.linspace(-1.5, 1.5, int(density_induced * 3), device=x_c.device).to(x_c.dtype)
     grid = grid1.view(1, -1, 1).expand(B, -1, 1)
     U = grid.shape[1]
     r_dim = sd["cntxt_to_induced.resizer.weight"].shape[0]
 
     def encode(x, y):        # ConvCNP.encode_globally (convnp.py:128-154)
         if x.shape[1] == 0:
-            R0 = torch.zeros(B, U, r_dim, dtype=x_t.dtype)
+            R0 = torch.zeros(B, U, r_dim, dtype=x_t.dtype, device=x_t.device)
         else:
             R0 = set_conv(sd, "cntxt_to_induced", x, grid, y)
         return cnn(sd, "induced_to_induced", R0, training, new_stats)
