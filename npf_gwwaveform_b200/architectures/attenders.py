@@ -16,7 +16,8 @@ from .blocks import MLP
 
 _USE_STASH = os.environ.get("NPFK_LN_STASH", "1") != "0"   # developer switch for A/B timing
 
-__all__ = ["get_attender", "DotAttender", "MultiheadAttender", "TransformerAttender"]
+__all__ = ["get_attender", "DotAttender", "MultiheadAttender", "TransformerAttender", "ScoreAttender",
+           "MultiplicativeAttender", "AdditiveAttender", "CosineAttender", "DistanceAttender"]
 
 
 def get_attender(attention, kq_size, value_size, out_size, **kwargs):
@@ -30,26 +31,34 @@ def get_attender(attention, kq_size, value_size, out_size, **kwargs):
         return MultiheadAttender(kq_size, value_size, out_size, **kwargs)
     if name == "transformer":
         return TransformerAttender(kq_size, value_size, out_size, **kwargs)
-    if name in ("multiplicative", "additive", "cosine", "manhattan", "euclidean", "weighted_dist"):
-        raise NotImplementedError(
-            f"attention={attention!r} is outside the B200 hot path (no 1-D waveform config uses it); "
-            "pass a callable Attender to plug in your own module."
-        )
+    # the remaining registry names (attention.py:60-86) are not on the waveform hot path: they run as plain PyTorch
+    # module composition on the GPU (plug-in row), with the reference's module layouts
+    if name == "multiplicative":
+        return MultiplicativeAttender(kq_size, value_size, out_size, **kwargs)
+    if name == "additive":
+        return AdditiveAttender(kq_size, value_size, out_size, **kwargs)
+    if name == "cosine":
+        return CosineAttender(kq_size, value_size, out_size, **kwargs)
+    if name == "manhattan":
+        return DistanceAttender(kq_size, value_size, out_size, p=1, **kwargs)
+    if name == "euclidean":
+        return DistanceAttender(kq_size, value_size, out_size, p=2, **kwargs)
+    if name == "weighted_dist":
+        return DistanceAttender(kq_size, value_size, out_size, is_weight=True, p=1, **kwargs)
     raise ValueError("Unknown attention method {}".format(attention))
 
 
-class DotAttender(nn.Module):
-    """softmax(q k^T / sqrt(d)) v  (single head), optional resizer when value_size != out_size."""
+class ScoreAttender(nn.Module):
+    """Generic attender (attention.py:92-170): ``context = dropout(attn(score(keys, queries))) @ values`` with
+    ``attn`` = softmax over keys when ``is_normalize`` else the raw logits, plus a resizer when value_size != out_size.
+    Subclasses give ``score(keys, queries) -> [B, Nq, Nk]``.  Plain PyTorch ops: this is the module-composition path for
+    everything the fused kernel does not recognise."""
 
-    def __init__(self, kq_size, value_size, out_size, is_scale=True, is_normalize=True, dropout=0):
+    def __init__(self, kq_size, value_size, out_size, is_normalize=True, dropout=0):
         super().__init__()
-        if not is_normalize:
-            raise NotImplementedError("is_normalize=False is not served by the fused attention kernel")
         self.kq_size, self.value_size, self.out_size = kq_size, value_size, out_size
-        self.is_scale, self.is_normalize = is_scale, is_normalize
+        self.is_normalize = is_normalize
         self.dropout = nn.Dropout(p=dropout) if dropout > 0 else nn.Identity()
-        if dropout > 0:
-            raise NotImplementedError("attention dropout is not implemented in the fused kernel")
         self.is_resize = value_size != out_size
         if self.is_resize:
             self.resizer = nn.Linear(value_size, out_size)
@@ -58,12 +67,124 @@ class DotAttender(nn.Module):
     def reset_parameters(self):
         weights_init(self)
 
+    def score(self, keys, queries, **kwargs):
+        raise NotImplementedError
+
+    def forward(self, keys, queries, values, **kwargs):
+        logits = self.score(keys, queries, **kwargs)
+        attn = logits.softmax(dim=-1) if self.is_normalize else logits
+        context = torch.bmm(self.dropout(attn), values)
+        return self.resizer(context) if self.is_resize else context
+
+
+def _dot_score(keys, queries, is_scale):
+    logits = torch.einsum("bkd,bqd->bqk", keys, queries)
+    return logits / math.sqrt(queries.size(-1)) if is_scale else logits
+
+
+class MultiplicativeAttender(ScoreAttender):
+    """Luong attention (attention.py:223-254): ``k . (W q)``; the inner ``dot`` keeps the reference's module tree."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.linear = nn.Linear(self.kq_size, self.kq_size, bias=False)
+        self.dot = DotAttender(*args, is_scale=False)
+        self.reset_parameters()
+
+    def score(self, keys, queries, **kwargs):
+        return _dot_score(keys, self.linear(queries), False)
+
+
+class AdditiveAttender(ScoreAttender):
+    """Bahdanau attention (attention.py:257-292): a tanh MLP over cat(k, q) for every (query, key) pair."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.mlp = MLP(self.kq_size * 2, 1, hidden_size=self.kq_size, activation=nn.Tanh())
+        self.reset_parameters()
+
+    def score(self, keys, queries, **kwargs):
+        B, Nq, D = queries.shape
+        Nk = keys.size(1)
+        # kept exactly as the reference has it (attention.py:284-290): the queries are expanded along dim 1 too, so the
+        # expression only type-checks when Nq == Nk and raises the same RuntimeError otherwise
+        k = keys.unsqueeze(1).expand(B, Nq, Nk, D)
+        q = queries.unsqueeze(1).expand(B, Nq, Nk, D)
+        return self.mlp(torch.cat((k, q), dim=-1)).squeeze(-1)
+
+
+class CosineAttender(ScoreAttender):
+    """attention.py:295-311.  The reference reshapes with ``view`` (no transpose) before ``CosineSimilarity(dim=1)``;
+    the same memory reinterpretation is kept so the numbers agree."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.similarity = nn.CosineSimilarity(dim=1)
+
+    def score(self, keys, queries, **kwargs):
+        B, Nq, D = queries.size()
+        Nk = keys.size(1)
+        return self.similarity(keys.contiguous().view(B, D, 1, Nk), queries.contiguous().view(B, D, Nq, 1))
+
+
+class DistanceAttender(ScoreAttender):
+    """negative squared p-norm of (optionally dimension-wise weighted) k - q (attention.py:314-372)"""
+
+    def __init__(self, *args, p=1, is_weight=False, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.p, self.is_weight = p, is_weight
+        if is_weight:
+            self.weighter = nn.Linear(self.kq_size, self.kq_size)
+        self.reset_parameters()
+
+    def score(self, keys, queries, **kwargs):
+        diff = keys.unsqueeze(1) - queries.unsqueeze(2)
+        if self.is_weight:
+            diff = self.weighter(diff)
+        return -torch.norm(diff, p=self.p, dim=-1) ** 2
+
+
+class DotAttender(nn.Module):
+    """softmax(q k^T / sqrt(d)) v  (single head), optional resizer when value_size != out_size."""
+
+    def __init__(self, kq_size, value_size, out_size, is_scale=True, is_normalize=True, dropout=0):
+        super().__init__()
+        self.kq_size, self.value_size, self.out_size = kq_size, value_size, out_size
+        self.is_scale, self.is_normalize = is_scale, is_normalize
+        self.dropout = nn.Dropout(p=dropout) if dropout > 0 else nn.Identity()
+        self.is_resize = value_size != out_size
+        if self.is_resize:
+            self.resizer = nn.Linear(value_size, out_size)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        weights_init(self)
+
+    def _fusable(self, keys, values):
+        """softmax-normalised, no attention dropout, value width == key width: what the flash kernel computes"""
+        return (self.is_normalize and isinstance(self.dropout, nn.Identity) and values.shape[-1] == keys.shape[-1]
+                and keys.is_cuda)
+
+    def score(self, keys, queries):
+        return _dot_score(keys, queries, self.is_scale)
+
     def attend(self, keys, queries, values, n_heads=1, delta_stash=None):
         d = queries.shape[-1] // n_heads
-        scale = 1.0 / math.sqrt(d) if self.is_scale else 1.0
-        if values.shape[-1] != keys.shape[-1]:
-            raise NotImplementedError("fused attention needs value_size == kq_size")
-        return K.mha(queries, keys, values, n_heads, scale, delta_stash)
+        if self._fusable(keys, values):
+            scale = 1.0 / math.sqrt(d) if self.is_scale else 1.0
+            return K.mha(queries, keys, values, n_heads, scale, delta_stash)
+        # module composition (attention.py:129-164 with the head split of :507-527): is_normalize=False, attention
+        # dropout, or value heads of another width than the key heads
+        B, Nq, Nk = queries.shape[0], queries.shape[1], keys.shape[1]
+        dv = values.shape[-1] // n_heads
+        qh = queries.reshape(B, Nq, n_heads, d).transpose(1, 2)
+        kh = keys.reshape(B, Nk, n_heads, d).transpose(1, 2)
+        vh = values.reshape(B, Nk, n_heads, dv).transpose(1, 2)
+        logits = qh @ kh.transpose(-1, -2)
+        if self.is_scale:
+            logits = logits / math.sqrt(d)
+        attn = self.dropout(logits.softmax(dim=-1) if self.is_normalize else logits)
+        return (attn @ vh).transpose(1, 2).reshape(B, Nq, n_heads * dv)
 
     def forward(self, keys, queries, values, **kwargs):
         ctx = self.attend(keys, queries, values)
