@@ -16,7 +16,11 @@
 //                           because the other key tiles of the same task add to the same rows.
 // scale is folded into the dQ / dK drains.  K, Q and dO are each needed K-major and MN-major; tf32 MN-major
 // operands only exist in the 32-byte-atom swizzle, so TMA loads them twice with two tensor maps (L2 hits).
-//   warp 0  TMA producer    warp 1  TMEM allocator + MMA issuer    warps 2..5 / 6..9  two softmax warpgroups (even / odd units)
+//   warp 0  TMA producer    warp 1  TMEM allocator + MMA issuer    warps 2.. : NSETS softmax warpgroups (unit u -> warpgroup u mod NSETS)
+// Default: two units in flight, four softmax warps per unit, dQ product with M = 128.  Measured alternatives kept behind
+// developer switches (C2 shape, same box): NPFK_ATTN_BWD_SETS=3 (three units in flight on a two-stage
+// ring: 4.62 vs 3.98 ms), NPFK_ATTN_BWD_WPU=8 (two warps per TMEM lane quarter: 4.32 vs 4.17 ms), NPFK_ATTN_BWD_DQ_M64=1
+// (dQ with UMMA M = 64, accumulator rows 16 j.. in lanes 0..15 of quarter j: 4.40 vs 4.19 ms).
 #include <math.h>
 
 #include "tc_common.cuh"
@@ -26,24 +30,34 @@ namespace tc {
 
 constexpr int kBK = 128;                       // keys per CTA (TMEM lanes)
 constexpr int kBQ = 64;                        // queries per half tile (UMMA N of S^T)
-constexpr int kBStages = 3;
-constexpr int kBThreads = 320;                 // TMA warp, MMA warp, two softmax warpgroups of 4 warps
 constexpr int kBStgBytes = kBK * kBQ * 4;      // 32 KB: dS^T staging, 2 blocks of [128 keys x 32 queries]
 constexpr int kBStgBlock = kBK * 128;          // 16 KB
 constexpr int kBTileQ = kBQ * 128;             // 8 KB: one half tile of a 32-float box
 constexpr int kBStageBytes = 4 * kBTileQ + 1024;   // Q(K-major) Q(MN) dO(K-major) dO(MN) + lse2/delta
 constexpr int kBTileK = kBK * 128;             // 16 KB
-constexpr int kBStgOff = 0;
-constexpr int kBStageOff = 2 * kBStgBytes;                       // 65536
-constexpr int kBKkmOff = kBStageOff + kBStages * kBStageBytes;   // 166912
-constexpr int kBKmnOff = kBKkmOff + kBTileK;
-constexpr int kBVOff = kBKmnOff + kBTileK;
-constexpr int kBBarOff = kBVOff + kBTileK;                       // 216064
-constexpr int kBNumBars = 1 + 2 * kBStages + 9;
-constexpr int kBSmem = 1024 + kBBarOff + kBNumBars * 8 + 16;
 constexpr uint32_t kBTmemCols = 512;
-constexpr uint32_t kBTmemAcc = 256;            // dK / dV accumulators
-constexpr uint32_t kBTmemDq = 384;             // two dQ accumulators of 32 columns
+
+// NSETS units (half tile x head) are in flight at once: one TMEM set (S^T | dP^T, 128 columns), one dS^T staging
+// buffer, one dQ accumulator and one softmax warpgroup per set.  Head dim 16 runs three sets on a two-stage Q/dO ring
+// (3 x 128 + 64 + 3 x 16 = 496 TMEM columns, 210 KB of shared memory); head dim 32 needs 32-column dQ buffers and
+// keeps two sets on a three-stage ring.
+// WPU = softmax warps per unit: 4 (a warp owns 32 keys x all 64 queries of the unit) or 8 (two warps share a TMEM lane
+// quarter and take 32 queries each, halving the serial softmax time of a unit: the unit chain is latency-bound).
+template <int NSETS, int WPU = 4>
+struct BwdCfg {
+    static constexpr int kStages = NSETS == 3 ? 2 : 3;
+    static constexpr int kThreads = 64 + 32 * WPU * NSETS;    // TMA warp, MMA warp, NSETS softmax groups of WPU warps
+    static constexpr int kStgOff = 0;
+    static constexpr int kStageOff = NSETS * kBStgBytes;
+    static constexpr int kKkmOff = kStageOff + kStages * kBStageBytes;
+    static constexpr int kKmnOff = kKkmOff + kBTileK;
+    static constexpr int kVOff = kKmnOff + kBTileK;
+    static constexpr int kBarOff = kVOff + kBTileK;
+    static constexpr int kNumBars = 1 + 2 * kStages + 4 * NSETS + 1;
+    static constexpr int kSmem = 1024 + kBarOff + kNumBars * 8 + 16;
+    static constexpr uint32_t kTmemAcc = NSETS * 128;           // dK / dV accumulators (64 columns)
+    static constexpr uint32_t kTmemDq = NSETS * 128 + 64;       // NSETS dQ accumulators of D columns
+};
 
 struct AttnBwdParams {
     float* dq;            // [B, Nq, E]  "+=" (zero-filled by the host wrapper)
@@ -54,8 +68,8 @@ struct AttnBwdParams {
     int64_t Nq, Nk, Nqp;
     float scale;
     int k_tiles, half_tiles, nsplit, tiles_per_split;
+    int dq_m64;           // dQ product with UMMA M = 64 (1: rows in lanes 0-15 of each quarter, 2: rows in lanes 0-63)
     int dbg;              // timing experiments only (NPFK_ATTN_DBG): 1 no softmax math, 2 no dQ MMAs, 4 no dV/dK MMAs, 8 no dq red, 16 no staging stores
-    int nh;               // UMMA N of the dV / dK / dQ products (16: one head, 32: whole box)
     int* g_abort;
 };
 
@@ -111,13 +125,18 @@ __device__ __forceinline__ float ex2_approx_b(float x) {
     return y;
 }
 
-template <int D>
-__global__ void __launch_bounds__(kBThreads, 1)
+template <int D, int NSETS, int WPU>
+__global__ void __launch_bounds__(BwdCfg<NSETS, WPU>::kThreads, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_constant__ CUtensorMap tmQm,
                    const __grid_constant__ CUtensorMap tmOk, const __grid_constant__ CUtensorMap tmOm,
                    const __grid_constant__ CUtensorMap tmKk, const __grid_constant__ CUtensorMap tmKm,
                    const __grid_constant__ CUtensorMap tmVk, const AttnBwdParams p) {
     constexpr int HB = 32 / D;     // heads per 32-float box
+    using Cfg = BwdCfg<NSETS, WPU>;
+    constexpr int kBStages = Cfg::kStages, kBStgOff = Cfg::kStgOff, kBStageOff = Cfg::kStageOff, kBKkmOff = Cfg::kKkmOff,
+                  kBKmnOff = Cfg::kKmnOff, kBVOff = Cfg::kVOff, kBBarOff = Cfg::kBarOff, kBNumBars = Cfg::kNumBars;
+    constexpr uint32_t kBTmemAcc = Cfg::kTmemAcc, kBTmemDq = Cfg::kTmemDq;
+    constexpr int NH = D;          // UMMA N of the dV / dK / dQ products: one head
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint64_t* bars = reinterpret_cast<uint64_t*>(base + kBBarOff);
@@ -126,10 +145,10 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
     bar.st_full = bars + 1;
     bar.st_empty = bar.st_full + kBStages;
     bar.s_full = bar.st_empty + kBStages;
-    bar.p_ready = bar.s_full + 2;
-    bar.dq_full = bar.s_full + 4;
-    bar.dq_empty = bar.s_full + 6;
-    bar.fin = bar.s_full + 8;
+    bar.p_ready = bar.s_full + NSETS;
+    bar.dq_full = bar.s_full + 2 * NSETS;
+    bar.dq_empty = bar.s_full + 3 * NSETS;
+    bar.fin = bar.s_full + 4 * NSETS;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + kBNumBars);
     volatile int* cta_abort = reinterpret_cast<volatile int*>(tmem_ptr + 1);
 
@@ -143,9 +162,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
     const int ht_begin = split * p.tiles_per_split;
     const int ht_end = min(p.half_tiles, ht_begin + p.tiles_per_split);
     const int U = (ht_end - ht_begin) * HB;                 // units = (half tile, head)
-    const int NH = p.nh;
-    const uint32_t head_mn_off = (NH == 16) ? 64u : 0u;     // byte offset of head 1 inside an MN-major row
-    const uint32_t head_col = (NH == 16) ? 0u : (uint32_t)D; // column offset of head 1 inside a 32-wide accumulator
+    constexpr uint32_t head_mn_off = 64u;                   // byte offset of head 1 inside an MN-major row (D = 16)
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmQk); prefetch_tmap(&tmQm); prefetch_tmap(&tmOk); prefetch_tmap(&tmOm);
@@ -155,11 +172,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
             mbar_init(&bar.st_full[i], 1);
             mbar_init(&bar.st_empty[i], 1);
         }
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < NSETS; ++i) {
             mbar_init(&bar.s_full[i], 1);
-            mbar_init(&bar.p_ready[i], 4);
+            mbar_init(&bar.p_ready[i], WPU);
             mbar_init(&bar.dq_full[i], 1);
-            mbar_init(&bar.dq_empty[i], 2);
+            mbar_init(&bar.dq_empty[i], p.dq_m64 == 1 ? 4 : 2);
         }
         mbar_init(bar.fin, 1);
         *cta_abort = 0;
@@ -183,11 +200,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                 const uint32_t st = i % kBStages, ph = (i / kBStages) & 1;
                 if (!mbar_wait(&bar.st_empty[st], ph ^ 1, cta_abort, p.g_abort, 41)) break;
                 uint8_t* s = base + kBStageOff + st * kBStageBytes;
-                mbar_arrive_expect_tx(&bar.st_full[st], 4u * kBTileQ + (uint32_t)HB * 512u);
+                const bool skip_mn = (p.dbg & 32) != 0;   // timing experiments only
+                mbar_arrive_expect_tx(&bar.st_full[st], (skip_mn ? 2u : 4u) * kBTileQ + (uint32_t)HB * 512u);
                 tma_load_3d(&tmQk, &bar.st_full[st], s, box * 32, ht * kBQ, b);
-                tma_load_3d(&tmQm, &bar.st_full[st], s + kBTileQ, box * 32, ht * kBQ, b);
+                if (!skip_mn) tma_load_3d(&tmQm, &bar.st_full[st], s + kBTileQ, box * 32, ht * kBQ, b);
                 tma_load_3d(&tmOk, &bar.st_full[st], s + 2 * kBTileQ, box * 32, ht * kBQ, b);
-                tma_load_3d(&tmOm, &bar.st_full[st], s + 3 * kBTileQ, box * 32, ht * kBQ, b);
+                if (!skip_mn) tma_load_3d(&tmOm, &bar.st_full[st], s + 3 * kBTileQ, box * 32, ht * kBQ, b);
                 for (int hb = 0; hb < HB; ++hb) {
                     const float* l2 = p.ws + (bh0 + hb) * p.Nqp + (int64_t)ht * kBQ;
                     bulk_load_1d(s + 4 * kBTileQ + hb * 512, l2, 256, &bar.st_full[st]);
@@ -199,7 +217,9 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
         if (U > 0 && elect_one()) {   // ------------------------------------------------------- MMA issuer
             const uint32_t idesc_s = make_idesc_tf32(kBQ, false, false);
             const uint32_t idesc_kv = make_idesc_tf32(NH, false, true);    // A from TMEM, B MN-major
-            const uint32_t idesc_dq = make_idesc_tf32(NH, true, true);     // A, B MN-major
+            // A, B MN-major; M = 64 reads only the 64 staged query rows (an M = 128 product fetches 64 more rows of A
+            // from shared memory that nobody uses: the kernel is shared-memory-bandwidth bound)
+            const uint32_t idesc_dq = make_idesc_tf32(NH, true, true, p.dq_m64 ? 64 : 128);
             const uint32_t kkm = smem_u32(base + kBKkmOff), kmn = smem_u32(base + kBKmnOff), vkm = smem_u32(base + kBVOff);
             const uint32_t stg0 = smem_u32(base + kBStgOff), stage0 = smem_u32(base + kBStageOff);
             // base descriptors; per-MMA operands are these plus a byte offset (sdesc_advance)
@@ -216,7 +236,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                     tc_fence_after();
                 }
                 const uint32_t koff = (uint32_t)(hb * D * 4);
-                const uint32_t tS = tmem_base + (uint32_t)(u & 1) * 128u;
+                const uint32_t tS = tmem_base + (uint32_t)(u % NSETS) * 128u;
                 const uint64_t dk = sdesc_advance(d_kkm, koff), dv = sdesc_advance(d_vkm, koff);
                 const uint64_t dq = sdesc_advance(d_stage_k, st * kBStageBytes + koff);
                 const uint64_t dd = sdesc_advance(dq, 2 * kBTileQ);
@@ -226,17 +246,19 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
 #pragma unroll
                 for (int s = 0; s < D / 8; ++s)
                     umma_tf32(tS + 64, sdesc_advance(dv, s * 32), sdesc_advance(dd, s * 32), idesc_s, s > 0);
-                umma_commit(&bar.s_full[u & 1]);
+                umma_commit(&bar.s_full[u % NSETS]);
                 return true;
             };
             auto role = [&]() {
                 if (!mbar_wait(bar.kv_full, 0, cta_abort, p.g_abort, 43)) return;
                 tc_fence_after();
-                if (!issue_s(0)) return;
+                // S^T / dP^T run NSETS - 1 units ahead of the products that consume P^T / dS^T
+                for (int u = 0; u < NSETS - 1 && u < U; ++u)
+                    if (!issue_s(u)) return;
                 for (int u = 0; u < U; ++u) {
-                    if (u + 1 < U && !issue_s(u + 1)) return;
+                    if (u + NSETS - 1 < U && !issue_s(u + NSETS - 1)) return;
                     const int i = u / HB, hb = u % HB;
-                    const uint32_t st = (uint32_t)i % kBStages, set = (uint32_t)u & 1, ph = ((uint32_t)u >> 1) & 1;
+                    const uint32_t st = (uint32_t)i % kBStages, set = (uint32_t)(u % NSETS), ph = ((uint32_t)(u / NSETS)) & 1;
                     if (!mbar_wait(&bar.p_ready[set], ph, cta_abort, p.g_abort, 44)) return;
                     if (!mbar_wait(&bar.dq_empty[set], ph ^ 1, cta_abort, p.g_abort, 45)) return;
                     tc_fence_after();
@@ -261,7 +283,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                     if (!(p.dbg & 2))
 #pragma unroll
                     for (int j = 0; j < kBK / 8; ++j)      // dQ = dS K   (rows 64..127 of the accumulator are unused)
-                        umma_tf32(tmem_base + kBTmemDq + set * 32u, sdesc_advance(d_ds, j * 1024), sdesc_advance(d_k, j * 1024),
+                        umma_tf32(tmem_base + kBTmemDq + set * (uint32_t)D, sdesc_advance(d_ds, j * 1024), sdesc_advance(d_k, j * 1024),
                                   idesc_dq, j > 0);
                     umma_commit(&bar.dq_full[set]);
                     if (hb == HB - 1) umma_commit(&bar.st_empty[st]);
@@ -273,7 +295,9 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
     } else {
         // ------------------------------------------------------------------------------ softmax / drain warps
         const int qd = warp & 3;                       // TMEM lane quarter this warp may access
-        const int wg = (warp - 2) >> 2;                // warpgroup: units of parity wg (= TMEM set, staging buffer, dQ buffer)
+        const int wg = (warp - 2) / WPU;               // softmax group: units u = wg mod NSETS (= TMEM set, staging buffer, dQ buffer)
+        const int half = ((warp - 2) % WPU) >> 2;      // WPU == 8: which 32 queries of the unit this warp takes
+        constexpr int NC = 8 / WPU;                    // 32-query chunks per warp
         const int kk = qd * 32 + lane;                 // key row inside the tile
         const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
         const float k2 = p.scale * 1.4426950408889634f;
@@ -286,21 +310,24 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
         };
         // dQ of unit u: rows 0..63 of the accumulator = the 64 queries of the half tile (lane quarters 0 and 1)
         auto drain_dq = [&](int u) -> bool {
-            const uint32_t set = (uint32_t)u & 1;
-            if (!wait_all(&bar.dq_full[set], ((uint32_t)u >> 1) & 1, 51)) return false;
-            if (qd < 2) {
+            const uint32_t set = (uint32_t)(u % NSETS);
+            if (!wait_all(&bar.dq_full[set], ((uint32_t)(u / NSETS)) & 1, 51)) return false;
+            // accumulator rows -> TMEM lanes: M = 128 / M = 64 "flat": query row r in lane r (quarters 0 and 1);
+            // M = 64 datapath layout: rows 16 j .. 16 j + 15 in lanes 0..15 of quarter j (all four quarters take part)
+            const bool quarters = p.dq_m64 == 1;
+            if ((quarters || qd < 2) && half == WPU / 4 - 1) {
                 tc_fence_after();
                 const int i = u / HB, hb = u % HB;
                 uint32_t r[D];
-                const uint32_t ta = lane_base + kBTmemDq + set * 32u + (uint32_t)hb * head_col;
+                const uint32_t ta = lane_base + kBTmemDq + set * (uint32_t)D;
                 if constexpr (D == 16) tmem_ld_32x16(ta, r);
                 else tmem_ld_32x32(ta, r);
                 tmem_ld_wait();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bar.dq_empty[set]);
-                const int64_t q = (int64_t)(ht_begin + i) * kBQ + kk;
-                if (q < p.Nq && !(p.dbg & 8)) {
+                const int64_t q = (int64_t)(ht_begin + i) * kBQ + (quarters ? qd * 16 + lane : kk);
+                if (q < p.Nq && !(p.dbg & 8) && (!quarters || lane < 16)) {
                     float* dst = p.dq + ((int64_t)b * p.Nq + q) * p.E + box * 32 + hb * D;
 #pragma unroll
                     for (int d4 = 0; d4 < D / 4; ++d4)
@@ -312,19 +339,19 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
         };
         auto role = [&]() {
             int last = -1;
-            for (int u = wg; u < U; u += 2) {
+            for (int u = wg; u < U; u += NSETS) {
                 const int i = u / HB, hb = u % HB;
-                const uint32_t set = (uint32_t)u & 1, st = (uint32_t)i % kBStages;
-                if (u >= 2 && !drain_dq(u - 2)) return;          // also frees staging[set]
+                const uint32_t set = (uint32_t)wg, st = (uint32_t)i % kBStages;
+                if (u >= NSETS && !drain_dq(u - NSETS)) return;          // also frees staging[set]
                 last = u;
                 if (!wait_all(&bar.st_full[st], ((uint32_t)i / kBStages) & 1, 52)) return;
-                if (!wait_all(&bar.s_full[set], ((uint32_t)u >> 1) & 1, 53)) return;
+                if (!wait_all(&bar.s_full[set], ((uint32_t)(u / NSETS)) & 1, 53)) return;
                 tc_fence_after();
                 const uint8_t* stats = base + kBStageOff + st * kBStageBytes + 4 * kBTileQ + hb * 512;
                 uint8_t* stg = base + kBStgOff + set * kBStgBytes + kk * 128;
                 const uint32_t tS = lane_base + set * 128u;
 #pragma unroll
-                for (int c = 0; c < ((p.dbg & 1) ? 0 : 2); ++c) {                    // 32 queries at a time
+                for (int c = half; c < ((p.dbg & 1) ? 0 : half + NC); ++c) {          // 32 queries at a time
                     uint32_t s[32], g[32];
                     tmem_ld_32x32(tS + c * 32, s);
                     tmem_ld_32x32(tS + 64 + c * 32, g);
@@ -374,9 +401,10 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
             tc_fence_after();
             const int64_t key = (int64_t)kt * kBK + kk;
 #pragma unroll
-            for (int hb = wg; hb < HB; hb += 2) {           // warpgroup g drains head g of the box
+            for (int hb = wg; hb < HB; hb += NSETS) {       // warpgroup g drains head g of the box
                 uint32_t rk[D], rv[D];
-                const uint32_t acc = lane_base + kBTmemAcc + (uint32_t)hb * 2u * (uint32_t)NH + (uint32_t)hb * head_col;
+                const uint32_t acc = lane_base + kBTmemAcc + (uint32_t)hb * 2u * (uint32_t)NH;
+                const bool do_k = WPU == 4 || half == 0, do_v = WPU == 4 || half == 1;   // two warps per lane quarter: one each
                 if constexpr (D == 16) {
                     tmem_ld_32x16(acc, rk);
                     tmem_ld_32x16(acc + NH, rv);
@@ -394,11 +422,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQk, const __grid_consta
                         const float4 c = make_float4(__uint_as_float(rv[4 * d4]), __uint_as_float(rv[4 * d4 + 1]),
                                                      __uint_as_float(rv[4 * d4 + 2]), __uint_as_float(rv[4 * d4 + 3]));
                         if (p.nsplit == 1) {
-                            *reinterpret_cast<float4*>(p.dk + off + 4 * d4) = a;
-                            *reinterpret_cast<float4*>(p.dv + off + 4 * d4) = c;
+                            if (do_k) *reinterpret_cast<float4*>(p.dk + off + 4 * d4) = a;
+                            if (do_v) *reinterpret_cast<float4*>(p.dv + off + 4 * d4) = c;
                         } else {
-                            red_add_v4(p.dk + off + 4 * d4, a.x, a.y, a.z, a.w);
-                            red_add_v4(p.dv + off + 4 * d4, c.x, c.y, c.z, c.w);
+                            if (do_k) red_add_v4(p.dk + off + 4 * d4, a.x, a.y, a.z, a.w);
+                            if (do_v) red_add_v4(p.dv + off + 4 * d4, c.x, c.y, c.z, c.w);
                         }
                     }
                 }
@@ -454,18 +482,19 @@ int attn_bwd_tc(const float* q, const float* k, const float* v, const float* out
     if (ns > p.half_tiles) ns = p.half_tiles;
     p.tiles_per_split = (int)((p.half_tiles + ns - 1) / ns);
     p.nsplit = (p.half_tiles + p.tiles_per_split - 1) / p.tiles_per_split;
-    static int nh_env = -1;
-    if (nh_env < 0) {
-        const char* e = getenv("NPFK_ATTN_BWD_NH");
-        nh_env = e ? atoi(e) : 0;
-    }
     static int dbg_env = -1;
     if (dbg_env < 0) {
         const char* e = getenv("NPFK_ATTN_DBG");
         dbg_env = e ? atoi(e) : 0;
     }
     p.dbg = dbg_env;
-    p.nh = (D == 16) ? ((nh_env == 32) ? 32 : 16) : 32;
+    static int m64_env = -1;
+    if (m64_env < 0) {
+        const char* e = getenv("NPFK_ATTN_BWD_DQ_M64");
+        m64_env = e ? atoi(e) : 0;
+    }
+    p.dq_m64 = m64_env;
+
     p.g_abort = abort_flag_ptr();
 
     // prep: delta and lse*log2e into the padded workspace; dq (and dk/dv when the queries are split) are "+="
@@ -479,26 +508,37 @@ int attn_bwd_tc(const float* q, const float* k, const float* v, const float* out
         cudaMemsetAsync(dk, 0, sizeof(float) * (size_t)B * Nk * E, st);
         cudaMemsetAsync(dv, 0, sizeof(float) * (size_t)B * Nk * E, st);
     }
-    static bool attr_done[2] = {false, false};
-    const int di = D == 16 ? 0 : 1;
-    if (!attr_done[di]) {
-        cudaError_t e = D == 16 ? cudaFuncSetAttribute(attn_bwd_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBSmem)
-                                : cudaFuncSetAttribute(attn_bwd_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBSmem);
-        if (e != cudaSuccess) {
-            set_error("attn_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-            return NPFK_ERR_CUDA;
-        }
-        attr_done[di] = true;
+    static int sets_env = -1, wpu_env = -1;
+    if (sets_env < 0) {
+        const char* e = getenv("NPFK_ATTN_BWD_SETS");
+        sets_env = (e && atoi(e) == 3) ? 3 : 2;
+        e = getenv("NPFK_ATTN_BWD_WPU");
+        wpu_env = (e && atoi(e) == 8) ? 8 : 4;
     }
     const int64_t grid = items * p.nsplit;
     if (grid > 2147483647LL) {
         set_error("attn_bwd_tc: grid too large");
         return NPFK_ERR_INVALID;
     }
-    if (D == 16)
-        attn_bwd_tc_kernel<16><<<(unsigned)grid, kBThreads, kBSmem, st>>>(tmQk, tmQm, tmOk, tmOm, tmKk, tmKm, tmVk, p);
-    else
-        attn_bwd_tc_kernel<32><<<(unsigned)grid, kBThreads, kBSmem, st>>>(tmQk, tmQm, tmOk, tmOm, tmKk, tmKm, tmVk, p);
+    auto launch = [&](auto kernel, int threads, int smem, bool& attr_done) -> int {
+        if (!attr_done) {
+            cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            if (e != cudaSuccess) {
+                set_error("attn_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+                return NPFK_ERR_CUDA;
+            }
+            attr_done = true;
+        }
+        kernel<<<(unsigned)grid, threads, smem, st>>>(tmQk, tmQm, tmOk, tmOm, tmKk, tmKm, tmVk, p);
+        return NPFK_OK;
+    };
+    static bool done[5] = {false, false, false, false, false};
+    if (D == 16 && sets_env == 3) rc = launch(attn_bwd_tc_kernel<16, 3, 4>, BwdCfg<3, 4>::kThreads, BwdCfg<3, 4>::kSmem, done[0]);
+    else if (D == 16 && wpu_env == 4) rc = launch(attn_bwd_tc_kernel<16, 2, 4>, BwdCfg<2, 4>::kThreads, BwdCfg<2, 4>::kSmem, done[1]);
+    else if (D == 16) rc = launch(attn_bwd_tc_kernel<16, 2, 8>, BwdCfg<2, 8>::kThreads, BwdCfg<2, 8>::kSmem, done[2]);
+    else if (wpu_env == 4) rc = launch(attn_bwd_tc_kernel<32, 2, 4>, BwdCfg<2, 4>::kThreads, BwdCfg<2, 4>::kSmem, done[3]);
+    else rc = launch(attn_bwd_tc_kernel<32, 2, 8>, BwdCfg<2, 8>::kThreads, BwdCfg<2, 8>::kSmem, done[4]);
+    if (rc) return rc;
     count_launch();
     return check_launch("attn_bwd_tc");
 }
