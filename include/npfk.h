@@ -70,6 +70,34 @@ int npfk_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx,
 int npfk_linear_bwd_fused(const float* g, int64_t ldg, const float* x, int64_t ldx, const float* w, int64_t ldw,
                           int masked, float* dx, int64_t lddx, float* dw, int64_t lddw, float* db, int64_t M, int N,
                           int K, int mode, void* stream);
+/* ---- K1: a ReLU-MLP chain of L <= 8 layers of 128 -> 128 as ONE kernel (NPFK_MODE_FAST only) ---------------
+ * Replaces MLP.forward (npf/architectures/mlp.py:95-109), the sum-merge of MergeFlatInputs
+ * (npf/architectures/encoders.py:175-183) and, with the tail, decode + sum_log_prob
+ * (npf/neuralproc/base.py:347-353,116; npf/losses.py:18-24).
+ *
+ *   h_0 = x ; h_{l+1} = act_l( h_l . w[l]^T + bias[l] + (l == res_layer ? res[m % res_rows] : 0) ),  act_l = relu when bit l
+ *   of relu_mask is set.  The activations stay in tensor memory between layers; out[l] != NULL asks for h_{l+1} in HBM
+ *   ([M,128] contiguous; what the backward pass needs, or the chain's result).  w[l]: [128,128] row-major, tf32-rounded
+ *   (npfk_round_tf32), contiguous.  w / bias / out are HOST arrays of L device pointers (bias, out and their entries may be
+ *   NULL).
+ *   Tail (head_w != NULL): suff[m,:] = h_L[m,:] . head_w^T + head_b  (head_w [2,128] fp32; suff [M,2] may be NULL), and with
+ *   y != NULL also sum_lp[m / T] += log N(y[m % y_rows]; suff[m,0], 0.01 + 0.99 softplus(suff[m,1]))  (sum_lp zeroed by
+ *   the caller).  Returns NPFK_ERR_UNSUPPORTED in NPFK_MODE_FP32 (run the layers through npfk_linear_fwd). */
+int npfk_mlp_chain_fwd(const float* x, int64_t ldx, int64_t M, int L, const float* const* w, const float* const* bias,
+                       int relu_mask, int res_layer, const float* res, int64_t ldres, int64_t res_rows, float* const* out,
+                       const float* head_w, const float* head_b, float* suff, const float* y, int64_t y_rows, int64_t T,
+                       float* sum_lp, int mode, void* stream);
+/* Backward of the tail above in one pass over h = h_L [M,128]: per row dsuff = dsuff_in (may be NULL) + dsum_lp[m / T] *
+ * d lp / d suff (dsum_lp may be NULL); g[m,:] = dsuff . head_w, zeroed where h <= 0 when `masked` (g may be NULL);
+ * dw[2,128] += dsuff^T . h ; db[2] += sum_m dsuff (either may be NULL). */
+int npfk_nll_head_bwd(const float* h, int64_t ldh, const float* head_w, const float* suff, const float* y, int64_t y_rows,
+                      int64_t T, const float* dsum_lp, const float* dsuff_in, int masked, float* g, float* dw, float* db,
+                      int64_t M, void* stream);
+/* Bytes of caller-provided workspace `op` needs for the given sizes (the library never allocates): NPFK_OP_MHA_BWD
+ * (B, Nq, H) -> delta_ws of npfk_mha_bwd; NPFK_OP_BN_STATS (C, -, -) -> scratch of npfk_bn_stats; 0 for every other op. */
+#define NPFK_OP_MHA_BWD 1
+#define NPFK_OP_BN_STATS 2
+int64_t npfk_workspace_bytes(int op, int64_t d0, int64_t d1, int64_t d2);
 /* dst[i] = round-to-nearest tf32(src[i]) (weights, before they meet tcgen05.mma.kind::tf32 which truncates) */
 int npfk_round_tf32(const float* src, float* dst, int64_t n, void* stream);
 /* != 0 when a tcgen05 kernel gave up on a bounded mbarrier wait since the last call (synchronises; tests only) */

@@ -66,15 +66,19 @@ class MLP(nn.Module):
         """True when the whole MLP can run as one K.mlp_chain node (ReLU, no dropout, no residual links)."""
         return isinstance(self.activation, nn.ReLU) and isinstance(self.dropout, nn.Identity) and not self.is_res
 
-    def forward(self, x, res=None, out_relu=False, x_is_relu=False, dy_premasked=False):
+    def forward(self, x, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None):
         """``res`` / ``out_relu`` fuse ``relu(res + MLP(x))`` (the sum-merge) into the last layer's epilogue.
-        ``x_is_relu`` / ``dy_premasked``: see kernels._MlpChainFn (ReLU backward fused across the sum-merge)."""
+        ``x_is_relu`` / ``dy_premasked``: see kernels._MlpChainFn (ReLU backward fused across the sum-merge).
+        ``nll=(y, T)`` (decoders only; see ``accepts_nll``): returns ``(out, sum_lp or None)``, the Gaussian
+        log-likelihood of y under the predictive distribution summed over the T rows of each task, evaluated in the
+        chain kernel's epilogue."""
         if self.is_plain_relu_chain():
             layers = [(self.to_hidden.weight, self.to_hidden.bias)]
             layers += [(lin.weight, lin.bias) for lin in self.linears]
             layers.append((self.out.weight, self.out.bias))
-            return K.mlp_chain(x, layers, res=res, out_relu=out_relu, x_is_relu=x_is_relu, dy_premasked=dy_premasked)
-        assert not (x_is_relu or dy_premasked)
+            return K.mlp_chain(x, layers, res=res, out_relu=out_relu, x_is_relu=x_is_relu, dy_premasked=dy_premasked,
+                               nll=nll)
+        assert not (x_is_relu or dy_premasked or nll is not None)
         h = self.dropout(self._hidden(self.to_hidden, x))
         for lin in self.linears:
             o = self._hidden(lin, h)
@@ -94,6 +98,10 @@ class DiscardIthArg(nn.Module):
 
     def filter_args(self, *args):
         return [a for j, a in enumerate(args) if j != self.i]
+
+    @property
+    def accepts_nll(self):
+        return type(self.destination) is MLP and self.destination.is_plain_relu_chain()
 
     def forward(self, *args, **kwargs):
         args = self.filter_args(*args)
@@ -131,18 +139,23 @@ class MergeFlatInputs(nn.Module):
     def reset_parameters(self):
         weights_init(self)
 
-    def _sum_merge(self, x1, x2):
+    @property
+    def accepts_nll(self):
+        """the decode tail (head + log-likelihood) can ride in flat_module's fused chain: forward(..., nll=(y, T))"""
+        return type(self.flat_module) is MLP and self.flat_module.is_plain_relu_chain()
+
+    def _sum_merge(self, x1, x2, nll=None):
         # Case A: x2 is one vector per (sample, task) replicated over the set dimension (CNP / LNP decoders,
         # reference np.py:103-110 expands it).  Run the resizer once per task and broadcast in the merge kernel.
         if x2.dim() == 4 and x1.dim() == 3 and _is_broadcast_over(x2, 2) and x1.shape[1] != 1:
             r = self.resizer(x2[:, :, 0, :])                       # [Z,B,C]
-            return K.bcast_add_relu(x1, r)
+            return K.bcast_add_relu(x1, r)     # (the caller applies flat_module, with nll when asked)
         # Case B: same rows (x2 possibly with a leading n_z dim that x1 is tiled over): fuse into the epilogue
         if x2.shape[-x1.dim():-1] == x1.shape[:-1] and x2.dim() in (x1.dim(), x1.dim() + 1):
             if self._fused_relu_bwd():
                 # merged feeds only flat_module, whose first dgrad masks with merged > 0: the resizer skips its own
                 merged = self.resizer(x2, res=x1, out_relu=True, dy_premasked=True)
-                return self.flat_module(merged, x_is_relu=True), True
+                return self.flat_module(merged, x_is_relu=True, nll=nll), True
             return self.resizer(x2, res=x1, out_relu=True)
         return torch.relu(x1 + self.resizer(x2))                     # exotic broadcasting: plain composition
 
@@ -151,15 +164,17 @@ class MergeFlatInputs(nn.Module):
         return (type(fm) is MLP and fm.is_plain_relu_chain() and self.resizer.is_plain_relu_chain()
                 and torch.is_grad_enabled())
 
-    def forward(self, x1, x2):
+    def forward(self, x1, x2, nll=None):
         if self.is_sum_merge:
-            merged = self._sum_merge(x1, x2)
+            merged = self._sum_merge(x1, x2, nll)
             if isinstance(merged, tuple):
                 return merged[0]
         else:
             if x2.dim() == x1.dim() + 1:
                 x1 = x1.unsqueeze(0).expand(x2.shape[0], *x1.shape)
             merged = torch.cat((x1, x2), dim=-1)
+        if nll is not None:
+            return self.flat_module(merged, nll=nll)
         return self.flat_module(merged)
 
 

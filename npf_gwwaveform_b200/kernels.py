@@ -271,6 +271,31 @@ def linear(x, w, b=None, res=None, relu=False, dx_stash=None):
     return _LinearFn.apply(x, w, b, res, relu, dx_stash)
 
 
+_CHAIN_DIM = 128      # the fused chain kernel (K1, csrc/tc_mlp_chain.cu) takes layers of 128 -> 128
+_CHAIN_MAX = 8
+
+
+def set_chain_fusion(flag: bool) -> None:
+    """Developer switch for A/B timing: False runs every MLP layer as its own GEMM launch (the round-1 path)."""
+    _state["chain_fusion"] = bool(flag)
+
+
+def _ptr_array(ts):
+    return (ctypes.c_void_p * len(ts))(*[None if t is None else t.data_ptr() for t in ts])
+
+
+def _chain_fwd(x, ldx, M, ws, bs, relus, res, res_rows, outs, head=None, nll=None):
+    """one launch of npfk_mlp_chain_fwd over consecutive 128 -> 128 layers; `outs[l]` None = that activation stays on
+    chip.  head = (w[2,128], b or None, suff[M,2]); nll = (y, y_rows, T, sum_lp)."""
+    L = len(ws)
+    relu_mask = sum(1 << l for l, r in enumerate(relus) if r)
+    hw, hb, suff = head if head is not None else (None, None, None)
+    y, y_rows, T, sum_lp = nll if nll is not None else (None, 0, 0, None)
+    LIB.call("npfk_mlp_chain_fwd", _p(x), ldx, M, L, _ptr_array(ws), _ptr_array(bs), relu_mask,
+             (L - 1) if res is not None else -1, _p(res), _CHAIN_DIM, res_rows, _ptr_array(outs), _p(hw), _p(hb), _p(suff),
+             _p(y), y_rows, T, _p(sum_lp), MODE_FAST, _st())
+
+
 class _MlpChainFn(Function):
     """A whole ReLU MLP (npf/architectures/mlp.py:95-109) as ONE autograd node.
 
@@ -281,12 +306,17 @@ class _MlpChainFn(Function):
       x_is_relu   the input x is itself a ReLU output -> dx is masked with x > 0 in the first layer's dgrad;
       dy_premasked  the consumer of y already masked the incoming gradient with y > 0 (it has x_is_relu set),
                   so the out_relu backward is the identity here.
+    In fast mode every run of >= 2 consecutive 128 -> 128 layers is ONE launch of the fused chain kernel
+    (npfk_mlp_chain_fwd: activations stay in tensor memory, only what backward needs is written), and a final 128 -> 2
+    layer (the decoder head) is evaluated in that kernel's epilogue.  ``nll = (y, T)`` additionally makes the node
+    return ``sum_t log N(y; loc, scale)`` per task as a second output (decode tail + sum_log_prob fused, north_star (4)).
     args = (x, res, w_1, b_1, ..., w_L, b_L); b_i may be None.
     """
 
     @staticmethod
-    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, x, res, *wb):
+    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, nll, x, res, *wb):
         require_cuda(x, res, *wb)
+        ctx.set_materialize_grads(False)
         n_layers = len(wb) // 2
         mode = _state["mode"]
         lead = x.shape[:-1]
@@ -298,50 +328,121 @@ class _MlpChainFn(Function):
         acts = [h]
         wvs, dims = [], []
         for i in range(n_layers):
-            w, b = wb[2 * i], wb[2 * i + 1]
-            N, Kd = w.shape
+            w = wb[2 * i]
             if mode == MODE_FAST:
                 wv = tf32_weight(w)
                 ldw = wv.shape[1]
             else:
                 wv, ldw = _weight_view(w)
+            wvs.append(wv)
+            dims.append([w.shape[0], w.shape[1], 0, ldw, 0])
+        training = any(ctx.needs_input_grad)
+        sq = [d[0] == _CHAIN_DIM and d[1] == _CHAIN_DIM and d[3] == _CHAIN_DIM for d in dims]
+        fuse_ok = (mode == MODE_FAST and _state.get("chain_fusion", True) and M >= 128)
+        resv, res_rows = None, 0
+        N_last = dims[-1][0]
+        if res is not None:
+            resv = _c(res)
+            res_rows = resv.numel() // N_last
+            if res_rows == 0 or M % max(res_rows, 1) != 0:
+                raise NpfkError(f"mlp: residual rows {res_rows} do not tile M={M}")
+        head_fused, suff, sum_lp, nll_saved = False, None, None, None
+        i = 0
+        while i < n_layers:
+            j = i
+            if fuse_ok and ldh % 4 == 0 and h.data_ptr() % 16 == 0:
+                while j < n_layers and sq[j] and j - i < _CHAIN_MAX:
+                    j += 1
+            # the decoder head: a final 128 -> 2 layer without ReLU or residual rides in the chain's epilogue
+            with_head = (j > i and j == n_layers - 1 and dims[j][0] == 2 and dims[j][1] == _CHAIN_DIM and res is None
+                         and not out_relu and wvs[j].is_contiguous())
+            if j - i >= 2 or (with_head and j - i >= 1):
+                relus = [True] * (j - i)
+                r_here = None
+                if j == n_layers:               # the run ends the chain: output activation and residual are the caller's
+                    relus[-1] = bool(out_relu)
+                    r_here = resv
+                outs = []
+                for l in range(i, j):
+                    keep = training or l == j - 1
+                    if with_head and l == j - 1 and not training:
+                        keep = False            # inference: nothing but the head's output leaves the chip
+                    outs.append(torch.empty(M, _CHAIN_DIM, device=x.device, dtype=torch.float32) if keep else None)
+                head = nl = None
+                if with_head:
+                    suff = torch.empty(M, 2, device=x.device, dtype=torch.float32)
+                    hb = wb[2 * j + 1]
+                    head = (wvs[j], _c(hb), suff)
+                    if nll is not None:
+                        yv, T = nll
+                        yv = _c(yv)
+                        sum_lp = torch.zeros(M // T, device=x.device, dtype=torch.float32)
+                        nl = (yv, yv.numel(), T, sum_lp)
+                        nll_saved = (yv, T)
+                _chain_fwd(h, ldh, M, wvs[i:j], [_c(wb[2 * l + 1]) for l in range(i, j)], relus, r_here, res_rows, outs,
+                           head, nl)
+                for l in range(i, j):
+                    dims[l][2] = ldh if l == i else _CHAIN_DIM
+                    dims[l][4] = res_rows if (r_here is not None and l == j - 1) else 0
+                    if l > i:
+                        acts.append(outs[l - i - 1])
+                h, ldh = outs[-1], _CHAIN_DIM
+                if with_head:
+                    acts.append(h)
+                    dims[j][2] = _CHAIN_DIM
+                    head_fused = True
+                    h, ldh = suff, 2
+                    i = j + 1
+                else:
+                    if j < n_layers:
+                        acts.append(h)
+                    i = j
+                continue
+            N, Kd = dims[i][0], dims[i][1]
             last = i == n_layers - 1
-            bv = _c(b)
-            resv, res_rows = None, 0
-            if last and res is not None:
-                resv = _c(res)
-                res_rows = resv.numel() // N
-                if res_rows == 0 or M % max(res_rows, 1) != 0:
-                    raise NpfkError(f"mlp: residual rows {res_rows} do not tile M={M}")
+            bv = _c(wb[2 * i + 1])
             y = torch.empty(M, N, device=x.device, dtype=torch.float32)
             if M > 0:
-                LIB.call("npfk_linear_fwd", _p(h), ldh, _p(wv), ldw, _p(bv), _p(resv), N, res_rows, _p(y), N, M, N, Kd,
-                         int(out_relu if last else True), mode, st)
-            wvs.append(wv)
-            dims.append((N, Kd, ldh, ldw, res_rows))
+                LIB.call("npfk_linear_fwd", _p(h), ldh, _p(wvs[i]), dims[i][3], _p(bv), _p(resv if last else None), N,
+                         res_rows if last else 0, _p(y), N, M, N, Kd, int(out_relu if last else True), mode, st)
+            dims[i][2] = ldh
+            dims[i][4] = res_rows if last else 0
             h, ldh = y, N
             if not last:
                 acts.append(y)
-        ctx.cfg = (out_relu, x_is_relu, dy_premasked, mode, M, n_layers, dims, res is not None,
-                   None if res is None else res.shape, [wb[2 * i + 1] is not None for i in range(n_layers)], x.shape)
+            i += 1
+        ctx.cfg = (out_relu, x_is_relu, dy_premasked, mode, M, n_layers, [tuple(d) for d in dims], res is not None,
+                   None if res is None else res.shape, [wb[2 * i + 1] is not None for i in range(n_layers)], x.shape,
+                   head_fused, nll_saved)
         ctx.wb = wb
-        ctx.save_for_backward(h if (out_relu and not dy_premasked) else None, *acts, *wvs)
-        return h.reshape(*lead, dims[-1][0])
+        if training:
+            ctx.save_for_backward(h if (out_relu and not dy_premasked) or head_fused else None, *acts, *wvs,
+                                  nll_saved[0] if nll_saved is not None else None)
+        out = h.reshape(*lead, dims[-1][0])
+        if nll is not None:
+            if sum_lp is None:      # the tail did not ride in the chain (fp32 mode, odd shapes): separate kernel
+                sum_lp = None
+            return out, sum_lp
+        return out
 
     @staticmethod
-    def backward(ctx, dy):
-        out_relu, x_is_relu, dy_premasked, mode, M, n_layers, dims, has_res, res_shape, has_b, x_shape = ctx.cfg
+    def backward(ctx, dy, dsum_lp=None):
+        (out_relu, x_is_relu, dy_premasked, mode, M, n_layers, dims, has_res, res_shape, has_b, x_shape, head_fused,
+         nll_saved) = ctx.cfg
         saved = ctx.saved_tensors
-        y_out, acts, wvs = saved[0], saved[1:1 + n_layers], saved[1 + n_layers:]
+        y_out, acts, wvs, y_nll = saved[0], saved[1:1 + n_layers], saved[1 + n_layers:1 + 2 * n_layers], saved[-1]
         st = _st()
         N_out = dims[-1][0]
-        g = _c(dy).reshape(M, N_out)
+        dev = acts[0].device
+        g = None if dy is None else _c(dy).reshape(M, N_out)
+        if g is None and not (head_fused and dsum_lp is not None):
+            g = torch.zeros(M, N_out, device=dev, dtype=torch.float32)
         if out_relu and not dy_premasked and M > 0:
             g2 = torch.empty_like(g)
             LIB.call("npfk_relu_bwd", _p(g), N_out, _p(y_out), N_out, _p(g2), N_out, M, N_out, st)
             g = g2
         dres = None
-        if has_res and ctx.needs_input_grad[4]:
+        if has_res and ctx.needs_input_grad[5]:
             res_rows = dims[-1][4]
             if res_rows == M:
                 dres = g.reshape(res_shape)
@@ -352,22 +453,35 @@ class _MlpChainFn(Function):
         for i in range(n_layers - 1, -1, -1):
             N, Kd, ldh, ldw, _ = dims[i]
             hin = acts[i]
-            need_w = ctx.needs_input_grad[5 + 2 * i] or (has_b[i] and ctx.needs_input_grad[6 + 2 * i])
-            need_dx = i > 0 or ctx.needs_input_grad[3]
+            need_w = ctx.needs_input_grad[6 + 2 * i] or (has_b[i] and ctx.needs_input_grad[7 + 2 * i])
+            need_dx = i > 0 or ctx.needs_input_grad[4]
             masked = i > 0 or x_is_relu
             dw = db = None
             if need_w:
-                sink_w = _grad_sink(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[5 + 2 * i] else None
-                sink_b = _grad_sink(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[6 + 2 * i] else None
-                dw = sink_w if sink_w is not None else torch.zeros(N, Kd, device=g.device, dtype=torch.float32)
+                sink_w = _grad_sink(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[6 + 2 * i] else None
+                sink_b = _grad_sink(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[7 + 2 * i] else None
+                dw = sink_w if sink_w is not None else torch.zeros(N, Kd, device=dev, dtype=torch.float32)
                 db = None
                 if has_b[i]:
-                    db = sink_b if sink_b is not None else torch.zeros(N, device=g.device, dtype=torch.float32)
+                    db = sink_b if sink_b is not None else torch.zeros(N, device=dev, dtype=torch.float32)
                 grads_wb[2 * i] = None if sink_w is not None else dw
                 grads_wb[2 * i + 1] = None if sink_b is not None else db
+            if head_fused and i == n_layers - 1 and M > 0:
+                # decoder tail: d(log-likelihood)/d(suff), the head's dgrad (+ ReLU mask of the layer below) and its
+                # weight / bias gradients in one pass over the last hidden activation
+                dx = torch.empty(M, Kd, device=dev, dtype=torch.float32) if need_dx else None
+                yv, T = nll_saved if nll_saved is not None else (None, 0)
+                use_lp = dsum_lp is not None and yv is not None
+                LIB.call("npfk_nll_head_bwd", _p(hin), ldh, _p(wvs[i]), _p(y_out), _p(y_nll if use_lp else None),
+                         y_nll.numel() if use_lp else 0, T if use_lp else 0,
+                         _p(_c(dsum_lp).reshape(-1)) if use_lp else None, _p(g), int(masked), _p(dx), _p(dw), _p(db), M, st)
+                g = dx
+                if not need_dx:
+                    break
+                continue
             if need_w and need_dx and M > 0:
                 # one pass over g and the saved input: dgrad (+ ReLU mask from hin) and wgrad together
-                dx = torch.empty(M, Kd, device=g.device, dtype=torch.float32)
+                dx = torch.empty(M, Kd, device=dev, dtype=torch.float32)
                 LIB.call("npfk_linear_bwd_fused", _p(g), N, _p(hin), ldh, _p(wvs[i]), ldw, int(masked), _p(dx), Kd,
                          _p(dw), Kd, _p(db), M, N, Kd, mode, st)
                 g = dx
@@ -377,21 +491,23 @@ class _MlpChainFn(Function):
             if not need_dx:
                 g = None
                 break
-            dx = torch.empty(M, Kd, device=g.device, dtype=torch.float32)
+            dx = torch.empty(M, Kd, device=dev, dtype=torch.float32)
             if M > 0:
                 LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wvs[i]), ldw, _p(hin) if masked else None, ldh if masked else 0,
                          _p(dx), Kd, M, N, Kd, mode, st)
             g = dx
-        dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[3]) else None
-        return (None, None, None, dx, dres, *grads_wb)
+        dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[4]) else None
+        return (None, None, None, None, dx, dres, *grads_wb)
 
 
-def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked=False):
-    """ReLU MLP over `layers` = [(weight, bias), ...] as a single autograd node (see _MlpChainFn)."""
+def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None):
+    """ReLU MLP over `layers` = [(weight, bias), ...] as a single autograd node (see _MlpChainFn).  ``nll=(y, T)``:
+    returns ``(out, sum_lp)`` where sum_lp[m // T] = sum of log N(y; loc, scale) over the T rows of a task, or
+    ``(out, None)`` when the tail could not ride in the fused chain (the caller then uses gauss_sum_log_prob)."""
     flat = []
     for w, b in layers:
         flat += [w, b]
-    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, x, res, *flat)
+    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, nll, x, res, *flat)
 
 
 # ------------------------------------------------------------------------------------------ broadcast merge

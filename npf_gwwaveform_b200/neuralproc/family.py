@@ -99,7 +99,7 @@ class NeuralProcessFamily(nn.Module, abc.ABC):
         if self.encoded_path == "latent":
             R = None
         R_trgt = self.trgt_dependent_representation(X_cntxt, z_samples, R, X_trgt)
-        p_yCc = self.decode(X_trgt, R_trgt)
+        p_yCc = self.decode(X_trgt, R_trgt, Y_trgt)
         return p_yCc, z_samples, q_zCc, q_zCct
 
     def _validate_inputs(self, X_cntxt, Y_cntxt, X_trgt, Y_trgt):
@@ -137,10 +137,18 @@ class NeuralProcessFamily(nn.Module, abc.ABC):
         )
 
     # ------------------------------------------------------------------ decode (base.py:327-367)
-    def decode(self, X_trgt, R_trgt):
-        suff = self.decoder(X_trgt, R_trgt)                      # [n_z, B, Nt, 2*y_dim]
+    def decode(self, X_trgt, R_trgt, Y_trgt=None):
+        """``Y_trgt`` (optional; the reference's decode has no such argument): when the targets are known, the
+        Gaussian log-likelihood summed over each task's targets is evaluated in the decoder kernel's epilogue and
+        attached to the returned distribution, where ``sum_log_prob`` picks it up (north_star (4))."""
         fused = isinstance(self.p_y_loc_transformer, nn.Identity) and isinstance(
             self.p_y_scale_transformer, _DefaultScaleTransform)
+        lp = None
+        if (fused and self.is_heteroskedastic and self.y_dim == 1 and Y_trgt is not None and R_trgt.dim() == 4
+                and getattr(self.decoder, "accepts_nll", False)):
+            suff, lp = self.decoder(X_trgt, R_trgt, nll=(Y_trgt, R_trgt.shape[2]))
+        else:
+            suff = self.decoder(X_trgt, R_trgt)                  # [n_z, B, Nt, 2*y_dim]
         if fused:
             loc, scale = K.loc_scale(suff)
         else:
@@ -155,6 +163,9 @@ class NeuralProcessFamily(nn.Module, abc.ABC):
         if fused and self.is_heteroskedastic:
             # lets the npf losses run Normal.log_prob + the target sum as one kernel straight from the logits
             p_yCc._npfk_suffstat = suff
+            if lp is not None:
+                p_yCc._npfk_sum_lp = (lp.view(R_trgt.shape[0], R_trgt.shape[1]), Y_trgt.data_ptr(), Y_trgt._version,
+                                      tuple(Y_trgt.shape))
         return p_yCc
 
     def set_extrapolation(self, min_max):
