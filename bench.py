@@ -204,6 +204,9 @@ class ClockSampler:
 KERNEL_FAMILIES = {
     "attention backward (tcgen05)": (["npfk_mha_bwd"], "tensor", "attn_bwd_tc_kernel"),
     "attention forward (tcgen05)": (["npfk_mha_fwd"], "tensor", "attn_fwd_tc_kernel"),
+    "MLP chain forward (K1: layers fused on chip, tcgen05 + TMEM-resident activations)": (
+        ["npfk_mlp_chain_fwd"], "hbm", "tc_mlp_chain_fwd_kernel"),
+    "decoder tail backward (log-likelihood + head dgrad/wgrad)": (["npfk_nll_head_bwd"], "hbm", "nll_head_bwd_kernel"),
     "linear forward (tcgen05 GEMM + bias/residual/ReLU epilogue)": (["npfk_linear_fwd"], "hbm", "tc_gemm_nt_kernel<0>"),
     "linear backward fused (dgrad + mask + wgrad)": (["npfk_linear_bwd_fused"], "hbm", "tc_linear_bwd_fused_kernel"),
     "linear dgrad": (["npfk_linear_bwd_dx"], "hbm", "tc_gemm_nt_kernel<1>"),

@@ -64,10 +64,16 @@ struct ChainParams {
     int64_t y_rows;                  // y index = row % y_rows (z-samples share the targets)
     int64_t T;                       // rows per task
     float* sum_lp;                   // [M / T], "+="
+    int dbg;                         // timing experiments only (NPFK_CHAIN_DBG): 1 = epilogues do nothing but the barrier hand-shake
     int* g_abort;
 };
 
 __device__ __forceinline__ float softplus_c(float x) { return x > 20.f ? x : log1pf(expf(x)); }
+// max(x, 0) rounded to the nearest tf32, ties away from zero: what cvt.rna.tf32.f32 gives for a non-negative input, as two
+// integer instructions (the compiler's cvt sequence carries an extra exponent test per element)
+__device__ __forceinline__ float relu_round_tf32(float x) {
+    return __uint_as_float((__float_as_uint(fmaxf(x, 0.f)) + 0x1000u) & 0xFFFFE000u);
+}
 
 __global__ void __launch_bounds__(kCThreads, 1)
 tc_mlp_chain_fwd_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p) {
@@ -232,20 +238,23 @@ tc_mlp_chain_fwd_kernel(const __grid_constant__ ChainMaps maps, const ChainParam
                 const bool has_res = l == p.res_layer;
                 const float* bl = sBias + l * 128;
                 float h0 = 0.f, h1 = 0.f;
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
+                // accumulator chunks are double-buffered in registers: the tcgen05.ld of chunk c + 1 is in flight while
+                // chunk c is processed (the loop is fully unrolled so that both buffers keep static register names)
+                uint32_t v[2][32];
+                if (!(p.dbg & 1)) tmem_ld_32x32(tD, v[0]);
+#pragma unroll
+                for (int c = 0; c < ((p.dbg & 1) ? 0 : 4); ++c) {
                     float4 r4[8];
-                    if (has_res && row_ok) {     // issued before the accumulator read so that the two latencies overlap
+                    if (has_res && row_ok) {     // issued before the accumulator wait so that the two latencies overlap
                         const float4* rp = reinterpret_cast<const float4*>(p.res + rrow * p.ldres + c * 32);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) r4[j] = __ldg(rp + j);
                     }
-                    uint32_t v[32];
-                    tmem_ld_32x32(tD + (uint32_t)(c * 32), v);
                     tmem_ld_wait();
+                    if (c + 1 < 4) tmem_ld_32x32(tD + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
                     float f[32];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + bl[c * 32 + j];
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[c & 1][j]) + bl[c * 32 + j];
                     if (has_res && row_ok) {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
@@ -254,12 +263,13 @@ tc_mlp_chain_fwd_kernel(const __grid_constant__ ChainMaps maps, const ChainParam
                     }
                     if (relu) {      // hidden activations are rounded to the nearest tf32 (as npfk_linear_fwd does), so the
 #pragma unroll               // truncation by the next layer's MMA is exact
-                        for (int j = 0; j < 32; ++j) f[j] = round_tf32(fmaxf(f[j], 0.f));
+                        for (int j = 0; j < 32; ++j) f[j] = relu_round_tf32(f[j]);
                     }
                     if (!last) {
+                        uint32_t o[32];
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(f[j]);
-                        tmem_st_32x32(tA + (uint32_t)(c * 32), v);
+                        for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(f[j]);
+                        tmem_st_32x32(tA + (uint32_t)(c * 32), o);
                     } else if (p.head_w) {
                         const float4* w0 = reinterpret_cast<const float4*>(sHead + c * 32);
                         const float4* w1 = reinterpret_cast<const float4*>(sHead + 128 + c * 32);
@@ -386,6 +396,12 @@ int tc_mlp_chain_fwd(const float* x, int64_t ldx, int64_t M, int L, const float*
     p.head_w = head_w; p.head_b = head_b; p.suff = suff;
     p.y = y; p.y_rows = y_rows; p.T = T > 0 ? T : 1; p.sum_lp = sum_lp;
     p.g_abort = abort_flag_ptr();
+    static int dbg_env = -1;
+    if (dbg_env < 0) {
+        const char* e = getenv("NPFK_CHAIN_DBG");
+        dbg_env = e ? atoi(e) : 0;
+    }
+    p.dbg = dbg_env;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(tc_mlp_chain_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCSmem);

@@ -314,7 +314,7 @@ class _MlpChainFn(Function):
     """
 
     @staticmethod
-    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, nll, x, res, *wb):
+    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, nll, grad_enabled: bool, x, res, *wb):
         require_cuda(x, res, *wb)
         ctx.set_materialize_grads(False)
         n_layers = len(wb) // 2
@@ -336,7 +336,7 @@ class _MlpChainFn(Function):
                 wv, ldw = _weight_view(w)
             wvs.append(wv)
             dims.append([w.shape[0], w.shape[1], 0, ldw, 0])
-        training = any(ctx.needs_input_grad)
+        training = bool(grad_enabled) and any(ctx.needs_input_grad)
         sq = [d[0] == _CHAIN_DIM and d[1] == _CHAIN_DIM and d[3] == _CHAIN_DIM for d in dims]
         fuse_ok = (mode == MODE_FAST and _state.get("chain_fusion", True) and M >= 128)
         resv, res_rows = None, 0
@@ -442,7 +442,7 @@ class _MlpChainFn(Function):
             LIB.call("npfk_relu_bwd", _p(g), N_out, _p(y_out), N_out, _p(g2), N_out, M, N_out, st)
             g = g2
         dres = None
-        if has_res and ctx.needs_input_grad[5]:
+        if has_res and ctx.needs_input_grad[6]:
             res_rows = dims[-1][4]
             if res_rows == M:
                 dres = g.reshape(res_shape)
@@ -453,13 +453,13 @@ class _MlpChainFn(Function):
         for i in range(n_layers - 1, -1, -1):
             N, Kd, ldh, ldw, _ = dims[i]
             hin = acts[i]
-            need_w = ctx.needs_input_grad[6 + 2 * i] or (has_b[i] and ctx.needs_input_grad[7 + 2 * i])
-            need_dx = i > 0 or ctx.needs_input_grad[4]
+            need_w = ctx.needs_input_grad[7 + 2 * i] or (has_b[i] and ctx.needs_input_grad[8 + 2 * i])
+            need_dx = i > 0 or ctx.needs_input_grad[5]
             masked = i > 0 or x_is_relu
             dw = db = None
             if need_w:
-                sink_w = _grad_sink(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[6 + 2 * i] else None
-                sink_b = _grad_sink(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[7 + 2 * i] else None
+                sink_w = _grad_sink(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[7 + 2 * i] else None
+                sink_b = _grad_sink(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[8 + 2 * i] else None
                 dw = sink_w if sink_w is not None else torch.zeros(N, Kd, device=dev, dtype=torch.float32)
                 db = None
                 if has_b[i]:
@@ -496,8 +496,8 @@ class _MlpChainFn(Function):
                 LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wvs[i]), ldw, _p(hin) if masked else None, ldh if masked else 0,
                          _p(dx), Kd, M, N, Kd, mode, st)
             g = dx
-        dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[4]) else None
-        return (None, None, None, None, dx, dres, *grads_wb)
+        dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[5]) else None
+        return (None, None, None, None, None, dx, dres, *grads_wb)
 
 
 def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None):
@@ -507,7 +507,9 @@ def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked
     flat = []
     for w, b in layers:
         flat += [w, b]
-    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, nll, x, res, *flat)
+    # Function.forward cannot see the caller's grad mode (needs_input_grad ignores no_grad): pass it, so that inference
+    # keeps nothing for a backward pass and writes only the chain's result
+    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, nll, torch.is_grad_enabled(), x, res, *flat)
 
 
 # ------------------------------------------------------------------------------------------ broadcast merge
@@ -1118,6 +1120,16 @@ class KernelTimer:
         if name == "npfk_linear_bwd_fused":
             M, N, Kd = a[12], a[13], a[14]
             return 4.0 * M * N * Kd, 4.0 * (M * N + 2 * M * Kd)
+        if name == "npfk_mlp_chain_fwd":
+            # algorithmic HBM bytes: the input tile, the residual, every activation the caller asked for, the head's [M,2]
+            M, L = a[2], a[3]
+            n_out = sum(1 for v in a[11] if v)
+            head = 1 if a[12] else 0
+            return (2.0 * M * 128 * 128 * L + 4.0 * M * 128 * head,
+                    4.0 * M * (128 * (1 + (1 if a[8] else 0) + n_out) + 3 * head))
+        if name == "npfk_nll_head_bwd":
+            M = a[13]
+            return 8.0 * M * 128, 4.0 * M * (128 * (2 if a[10] else 1) + 4)
         if name == "npfk_mha_fwd":
             B, Nq, Nk, H, D = a[5:10]
             return 4.0 * B * H * Nq * Nk * D, 4.0 * B * H * D * (2 * Nq + 2 * Nk)
