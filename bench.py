@@ -61,6 +61,10 @@ def parse():
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
                     help="replay forward+loss+backward as one CUDA graph (auto = on); off = eager launches only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: fixed tasks per GPU; strong: BASELINE.json's global batch split over the ranks")
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="skip the secondary block (configs[2] and configs[3] measured after the headline workload)")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline leg")
     return ap.parse_args()
 
@@ -227,10 +231,15 @@ def ncu_traffic():
     return {}
 
 
-def build_roofline(ksum, total_ms, args, pk, B, Nt):
+def build_roofline(ksum, total_ms, args, pk, B, Nt, workload=None, steps=None):
     """`roofline` object of the JSON line: the dominant kernel family (largest share of the timed step) against the
     roofline that bounds it, plus the same figures for every other timed family under `families`."""
-    traffic = ncu_traffic() if args.workload == "attncnp_c2" else {}
+    workload = workload or args.workload
+    steps = steps or args.steps
+    all_traffic = ncu_traffic()
+    # profiles/ncu_traffic.json: {device kernel: {...}} captured at the C2 shapes, plus {"<workload>": {kernel: {...}}}
+    # sections for the captures made at other workloads' shapes
+    traffic = all_traffic.get(workload, all_traffic if workload == "attncnp_c2" else {})
     fams = {}
     for fam, (names, bound, dev_kernel) in KERNEL_FAMILIES.items():
         ms = sum(ksum.get(n, {}).get("ms_total", 0.0) for n in names)
@@ -241,7 +250,7 @@ def build_roofline(ksum, total_ms, args, pk, B, Nt):
         nbytes = sum(ksum.get(n, {}).get("bytes_total", 0.0) for n in names)
         tfs = flops / (ms * 1e-3) / 1e12
         gbs = nbytes / (ms * 1e-3) / 1e9
-        e = {"bound": bound, "launches_timed": calls, "avg_launch_ms": ms / calls, "ms_per_step": ms / args.steps,
+        e = {"bound": bound, "launches_timed": calls, "avg_launch_ms": ms / calls, "ms_per_step": ms / steps,
              "share_of_step": ms / total_ms, "device_kernel": dev_kernel}
         if bound == "tensor":
             # peak = measured dense bf16 (MEASURED_PEAKS.json); the kernels run kind::tf32, whose dense peak is half
@@ -261,7 +270,7 @@ def build_roofline(ksum, total_ms, args, pk, B, Nt):
     out = {"kernel": dom}
     out.update(fams[dom])
     out["peak_source"] = pk["source"]
-    alg = 3 * FLOPS_FWD_PER_TARGET[args.workload] * B * Nt / (total_ms / args.steps * 1e-3) / 1e12
+    alg = 3 * FLOPS_FWD_PER_TARGET[workload] * B * Nt / (total_ms / steps * 1e-3) / 1e12
     out["whole_step"] = {"algorithmic_tflops": alg, "frac_of_peak": alg / pk["tflops"]}
     out["families"] = {f: e for f, e in fams.items() if f != dom}
     return out
@@ -365,6 +374,25 @@ def run_infer(args):
     for _ in range(2):
         step_e2e()
     e2e_ms = timed_loop(step_e2e, args.steps) / args.steps
+
+    # the product-level driver of the sweep (npf_gwwaveform_b200.utils.predict.predict_sharded): this rank's shard of
+    # world * B * n_chunks tasks, chunk by chunk from pinned host memory (H2D of the next chunk overlapped with the
+    # current forward), per-task summaries kept on the device and copied to the host once at the end; eager launches
+    from npf_gwwaveform_b200.utils.predict import predict_sharded
+
+    n_chunks = 4
+    host_y = dict(host)
+
+    def source(lo, hi):
+        for _ in range(lo, hi, B):
+            yield host_y
+
+    def sweep():
+        summ, _ = predict_sharded(model, source, n_tasks=world * B * n_chunks, chunk=B, rank=rank, world_size=world)
+        return summ.cpu()
+
+    sweep()
+    sweep_ms = timed_loop(sweep, 1)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -390,6 +418,10 @@ def run_infer(args):
                 "h2d_bytes_per_step": h2d_bytes * world, "d2h_bytes_per_step": 4 * B * world,
                 "path": "pinned host inputs -> static device inputs -> model.forward (eval) -> per-task mean predictive "
                         "std to host"},
+        "sweep": {"api": "npf_gwwaveform_b200.utils.predict.predict_sharded", "tasks": world * B * n_chunks, "chunk": B,
+                  "value": world * B * n_chunks * Nt / (sweep_ms * 1e-3), "unit": UNIT, "ms": sweep_ms,
+                  "path": "shard_range over ranks -> chunks from pinned host memory, H2D double-buffered on a copy stream -> "
+                          "model.forward (eval, eager launches) -> per-task summary on device -> one D2H of the summaries"},
         "gpu_launches": launches, "roofline": roofline,
     }
     emit(line)
@@ -398,43 +430,50 @@ def run_infer(args):
 
 
 # ------------------------------------------------------------------------------------------ product arm
-def run_ours(args):
+# strong scaling: the GLOBAL batch BASELINE.json names is fixed and split over the ranks; a rank walks its share in
+# micro-batches of at most the per-GPU batch of the weak-scaling run (gradient accumulation inside the captured step)
+GLOBAL_BATCH = {"attncnp_c2": 256, "convcnp_c3": 256, "attnlnp_c4": 128, "cnp_c1": 64}
+
+
+def measure_training(args, workload, dev, rank, world, scaling, steps, warmup, with_timer=True, with_e2e=True):
+    """Build the model of `workload`, run `warmup` + `steps` optimisation steps (eager, timed per kernel), capture the
+    step into CUDA graphs and time `steps` replays.  Returns a dict of raw measurements (rank-0 view; the timings are
+    the max over ranks)."""
     import torch
     import torch.distributed as dist
 
     import npf_gwwaveform_b200 as npf
     from npf_gwwaveform_b200 import kernels as Kn
-    from npf_gwwaveform_b200.neuralproc import set_lazy_validation
-    from npf_gwwaveform_b200.training import FlatAdamTrainer
+    from npf_gwwaveform_b200.training import FlatAdamTrainer, shard_range
     from util_models import build_product, chirp_batch
 
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py (product arm) needs a CUDA device: there is no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL prints its version banner (NCCL_DEBUG=VERSION/WARN/INFO) on stdout: keep stdout to the ONE JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/npf_nccl_%h_%p.log")
-        dist.init_process_group("nccl", device_id=dev)
-
-    model_name, B, Nc, Nt, nz = WORKLOADS[args.workload]
-    if args.tasks_per_gpu:
+    model_name, B, Nc, Nt, nz = WORKLOADS[workload]
+    if args.tasks_per_gpu and workload == args.workload:
         B = args.tasks_per_gpu
-    npf.set_mode(args.mode)
-    set_lazy_validation(True)                       # range flag still computed every step, read one step late
+    micro = 1
+    if scaling == "strong":
+        G = GLOBAL_BATCH[workload]
+        assert G % world == 0, f"global batch {G} does not split over {world} ranks"
+        per_rank = G // world
+        micro = max(1, (per_rank + B - 1) // B)
+        assert per_rank % micro == 0
+        B = per_rank // micro
     torch.manual_seed(0)                            # identical initial weights on every rank
     model = build_product(model_name, 128, nz=nz).to(dev).train()
     crit = (npf.ELBOLossLNPF if "LNP" in model_name else npf.CNPFLoss)().train()
     trainer = FlatAdamTrainer(model, crit, lr=1e-3)
 
-    # per-rank synthetic shard (seed 1234 + rank), resident in HBM for `value`, pinned on the host for `e2e`
-    host = {k: v.pin_memory() for k, v in chirp_batch(B, Nc, Nt, 1234 + rank).items()}
-    resident = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
+    # synthetic shard resident in HBM for `value`, pinned on the host for `e2e`.  weak: every rank draws its own tasks
+    # (seed 1234 + rank); strong: rank r takes its slice of ONE global batch (seed 1234), micro-batch by micro-batch
+    if scaling == "strong":
+        whole = chirp_batch(GLOBAL_BATCH[workload], Nc, Nt, 1234)
+        lo, hi = shard_range(GLOBAL_BATCH[workload], rank, world)
+        hosts = [{k: v[lo + i * B:lo + (i + 1) * B].contiguous().pin_memory() for k, v in whole.items()} for i in range(micro)]
+        del whole
+    else:
+        hosts = [{k: v.pin_memory() for k, v in chirp_batch(B, Nc, Nt, 1234 + rank).items()}]
+    residents = [{k: v.to(dev, non_blocking=True) for k, v in h.items()} for h in hosts]
+    h2d_bytes = sum(v.numel() * v.element_size() for h in hosts for v in h.values())
 
     def barrier():
         if world > 1:
@@ -454,60 +493,158 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    def step_resident():
-        return trainer.step(resident)
+    def step_eager():        # micro > 1: eager warm-up steps treat every micro-batch as a step of its own
+        loss = None
+        for r in residents:
+            loss = trainer.step(r)
+        return loss
 
-    loss_host = torch.zeros(1).pin_memory()
-
-    def step_e2e():
-        batch = {k: v.to(dev, non_blocking=True) for k, v in host.items()}      # H2D of this step's inputs
-        loss = trainer.step(batch)
-        loss_host.copy_(loss.reshape(1), non_blocking=False)                    # D2H read of the step's result
-        return loss_host
-
-    for _ in range(max(args.warmup, 3)):
-        step_resident()
-    timed_names = [n for ns in KERNEL_FAMILIES.values() for n in ns[0]]
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    for _ in range(max(warmup, 3)):
+        step_eager()
+    timed_names = [n for ns in KERNEL_FAMILIES.values() for n in ns[0]] if with_timer else []
     n0 = Kn.launch_count()
     with Kn.KernelTimer(timed_names) as kt:
-        total_ms = timed_loop(step_resident, args.steps)
+        total_ms = timed_loop(step_eager, steps)
     launches = Kn.launch_count() - n0
-    ksum = kt.summary()
-    eager_ms_per_step = total_ms / args.steps
-    ms_per_step = eager_ms_per_step
-    use_graph = args.graph in ("on", "auto")
-    if use_graph:
-        # the same step with forward + loss + backward replayed as ONE CUDA graph (the kernels and their order are
-        # those of the eager loop above, which also provides the per-kernel CUDA-event times for the roofline)
-        trainer.capture(resident)
+    res = dict(workload=workload, model=model_name, tasks_per_gpu=B * micro, micro_batches=micro, micro_batch=B, Nc=Nc, Nt=Nt,
+               nz=nz, ksum=kt.summary(), eager_total_ms=total_ms, eager_ms_per_step=total_ms / steps, launches=launches,
+               h2d_bytes=h2d_bytes, graph=False)
+    ms_per_step = res["eager_ms_per_step"]
+    step_resident = step_eager
+    loss_host = torch.zeros(1).pin_memory()
 
-        def step_resident_graph():
-            return trainer.step_graphed(resident)
+    def step_e2e_eager():
+        loss = None
+        for h in hosts:
+            batch = {k: v.to(dev, non_blocking=True) for k, v in h.items()}      # H2D of this step's inputs
+            loss = trainer.step(batch)
+        loss_host.copy_(loss.reshape(1), non_blocking=False)                        # D2H read of the step's result
+        return loss_host
+
+    step_e2e = step_e2e_eager
+    if args.graph in ("on", "auto"):
+        # the same step (zero + forward + loss + backward + bucketed NCCL all-reduce + Adam) replayed as CUDA graphs;
+        # the kernels and their order are those of the eager loop above, which also gave the per-kernel event times
+        trainer.capture(residents[0], micro_batches=micro)
+
+        def step_graph():
+            loss = None
+            for i, r in enumerate(residents):
+                loss = trainer.step_graphed(r, first=i == 0, last=i == micro - 1)
+            return loss
 
         def step_e2e_graph():
-            # input pipeline: the H2D copy of the next step's batch (same pinned tensors here) was started while the
-            # previous step ran; this step waits for it, copies it D2D into the graph's static inputs, replays, and
-            # starts the next H2D before reading the loss back - one H2D and one D2H per step inside the timed region
-            loss = trainer.step_graphed(host)
-            trainer.prefetch(host)
+            # input pipeline: the H2D copy of the next (micro-)batch was started while the previous one computed; this
+            # one waits for it, copies it D2D into the graph's static inputs, replays, and starts the next H2D before
+            # the loss is read back: every input byte crosses PCIe once per step inside the timed region
+            loss = None
+            for i, h in enumerate(hosts):
+                loss = trainer.step_graphed(h, first=i == 0, last=i == micro - 1)
+                trainer.prefetch(hosts[(i + 1) % micro])
             loss_host.copy_(loss.reshape(1), non_blocking=False)
             return loss_host
 
         for _ in range(3):
-            step_resident_graph()
-        ms_per_step = timed_loop(step_resident_graph, args.steps) / args.steps
-        step_e2e, step_resident = step_e2e_graph, step_resident_graph
-    clocks = sampler.stop() if rank == 0 else {}
-    value = world * B * Nt / (ms_per_step * 1e-3)
+            step_graph()
+        ms_per_step = timed_loop(step_graph, steps) / steps
+        step_e2e, step_resident = step_e2e_graph, step_graph
+        res["graph"] = True
+    res["ms_per_step"] = ms_per_step
+    res["value"] = world * B * micro * Nt / (ms_per_step * 1e-3)
+    if with_e2e:
+        for _ in range(2):
+            step_e2e()
+        e2e_ms = timed_loop(step_e2e, steps) / steps
+        res["e2e_ms"] = e2e_ms
+        res["e2e_value"] = world * B * micro * Nt / (e2e_ms * 1e-3)
+    res["final_loss"] = float(step_resident().item())
+    res["trainer"] = trainer
+    res["residents"] = residents
+    return res
 
-    for _ in range(2):
-        step_e2e()
-    e2e_ms = timed_loop(step_e2e, args.steps) / args.steps
-    e2e_value = world * B * Nt / (e2e_ms * 1e-3)
-    final_loss = float(step_resident().item())
+
+def dp_check(res, dev, rank, world):
+    """NCCL correctness of the data-parallel step: the all-reduced mean gradient of the ranks' shards must equal the
+    gradient rank 0 gets by walking ALL shards itself on the same weights (shards gathered over NCCL, no optimiser
+    step).  BatchNorm models use per-replica statistics (reference semantics on a shard), which this reproduces shard by
+    shard.  Returns the relative L2 difference (rank 0) or None."""
+    import torch
+    import torch.distributed as dist
+
+    trainer = res["trainer"]
+    model, crit = trainer.model, trainer.criterion
+    shard = res["residents"][0]
+    was = {n: b.clone() for n, b in model.named_buffers()}      # BatchNorm running statistics must not drift
+
+    def grad_of(batch):
+        trainer.flat_grad.zero_()
+        crit(model(**batch), batch["Y_trgt"]).backward()
+        return trainer.flat_grad.clone()
+
+    g_local = grad_of(shard)
+    g_dp = g_local.clone()
+    dist.all_reduce(g_dp, op=dist.ReduceOp.SUM)
+    g_dp /= world
+    gathered = {k: [torch.empty_like(v) for _ in range(world)] for k, v in shard.items()}
+    for k, v in shard.items():
+        dist.all_gather(gathered[k], v.contiguous())
+    out = None
+    if rank == 0:
+        g_ref = torch.zeros_like(g_local)
+        for r in range(world):
+            g_ref += grad_of({k: gathered[k][r] for k in shard})
+        g_ref /= world
+        out = float((g_dp - g_ref).norm() / g_ref.norm().clamp_min(1e-30))
+    trainer.flat_grad.zero_()
+    with torch.no_grad():
+        for n, b in model.named_buffers():
+            b.copy_(was[n])
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import npf_gwwaveform_b200 as npf
+    from npf_gwwaveform_b200.neuralproc import set_lazy_validation
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (product arm) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL prints its version banner (NCCL_DEBUG=VERSION/WARN/INFO) on stdout: keep stdout to the ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/npf_nccl_%h_%p.log")
+        dist.init_process_group("nccl", device_id=dev)
+    npf.set_mode(args.mode)
+    set_lazy_validation(True)                       # range flag still computed every step, read one step late
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    res = measure_training(args, args.workload, dev, rank, world, args.scaling, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else {}
+    check = dp_check(res, dev, rank, world) if world > 1 else None
+    res.pop("trainer").close()
+    res.pop("residents")
+    torch.cuda.empty_cache()
+
+    # secondary block: the other training configurations BASELINE.json names, measured in the same process so that the
+    # driver's 1/2/4/8-GPU run covers them: configs[2] ConvCNP-UNet at 32 tasks per GPU (= batch 256 over 8 GPUs, weak
+    # scaling) and configs[3] AttnLNP with the global batch fixed at 128 (strong scaling, micro-batches of 16 tasks)
+    secondary = {}
+    if args.workload == "attncnp_c2" and not args.no_secondary:
+        for wl, sc in (("convcnp_c3", "weak"), ("attnlnp_c4", "strong")):
+            r2 = measure_training(args, wl, dev, rank, world, sc, max(3, args.steps // 2), 3, with_timer=True, with_e2e=False)
+            r2.pop("trainer").close()
+            r2.pop("residents")
+            torch.cuda.empty_cache()
+            secondary[wl] = (r2, sc)
 
     if rank != 0:
         if world > 1:
@@ -515,31 +652,50 @@ def run_ours(args):
         return
 
     pk = peaks()
-    roofline = build_roofline(ksum, total_ms, args, pk, B, Nt)
+    B, Nc, Nt, nz = res["tasks_per_gpu"], res["Nc"], res["Nt"], res["nz"]
+    roofline = build_roofline(res["ksum"], res["eager_total_ms"], args, pk, B, Nt, args.workload)
+    use_graph = res["graph"]
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": res["ms_per_step"], "higher_is_better": True,
+        "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f32" if args.mode == "fp32" else "tf32 operands (tcgen05 kind::tf32), f32 accumulate, f32 storage",
         "data": "synthetic",
         "config": {"workload": WORKLOAD_TEXT[args.workload], "tasks_per_gpu": B, "global_batch": B * world,
+                   "micro_batches_per_step": res["micro_batches"],
                    "n_context": Nc, "n_target": Nt, "n_z": nz, "mode": args.mode,
                    "step": "forward + loss + backward + gradient all-reduce + Adam",
-                   "launch": ("forward+loss+backward replayed as one CUDA graph; all-reduce and Adam launched eagerly"
-                              if use_graph else "eager launches"),
-                   "eager_ms_per_step": eager_ms_per_step,
+                   "launch": ("the whole step (zero grads, forward, loss, backward, bucketed NCCL all-reduce forked off in the "
+                              "middle of backward, Adam) replayed as one CUDA graph" if use_graph else "eager launches"),
+                   "eager_ms_per_step": res["eager_ms_per_step"],
                    "parallelism": f"data-parallel over tasks x{world}",
                    "l2": "activations streamed per step (several GB) exceed the 126 MB L2; no explicit flush"},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d_bytes * world,
-                "d2h_bytes_per_step": 4 * world,
+        "e2e": {"value": res["e2e_value"], "unit": UNIT, "ms_per_step": res["e2e_ms"],
+                "h2d_bytes_per_step": res["h2d_bytes"] * world, "d2h_bytes_per_step": 4 * world,
                 "path": ("pinned host tensors -> H2D on a copy stream into a staging set while the previous step runs "
                          "(FlatAdamTrainer.prefetch) -> D2D into the graph's static inputs -> graph replay (forward, "
-                         "loss, backward) -> all-reduce -> Adam -> loss to host (blocking D2H every step)") if use_graph
+                         "loss, backward, all-reduce, Adam) -> loss to host (blocking D2H every step)") if use_graph
                 else "pinned host tensors -> .to(device) -> model(**batch) -> criterion -> backward -> Adam -> loss to host"},
-        "gpu_launches": launches,
+        "gpu_launches": res["launches"],
         "roofline": roofline,
-        "final_loss": final_loss,
+        "final_loss": res["final_loss"],
     }
+    if check is not None:
+        line["dp_check"] = {"what": "||allreduce(mean of shard gradients) - gradient of all shards on rank 0|| / ||.||",
+                            "rel_l2": check, "ok": bool(check < 5e-3)}
+        assert check < 5e-3, f"data-parallel gradient differs from the single-rank gradient: {check}"
+    for wl, (r2, sc) in secondary.items():
+        secondary[wl] = {
+            "workload": WORKLOAD_TEXT[wl], "scaling": sc, "value": r2["value"], "unit": UNIT, "ms_per_step": r2["ms_per_step"],
+            "tasks_per_gpu": r2["tasks_per_gpu"], "global_batch": r2["tasks_per_gpu"] * world,
+            "micro_batches_per_step": r2["micro_batches"], "eager_ms_per_step": r2["eager_ms_per_step"],
+            "gpu_launches": r2["launches"], "final_loss": r2["final_loss"],
+            "roofline": build_roofline(r2["ksum"], r2["eager_total_ms"], args, pk, r2["tasks_per_gpu"], r2["Nt"], wl,
+                                       steps=max(3, args.steps // 2)),
+        }
+    if secondary:
+        line["secondary"] = secondary
     if world == 1 and not args.no_cpu_baseline:
         rate, desc, cores, _ = cpu_reference_rate(args.workload, seconds=args.cpu_seconds)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}

@@ -201,60 +201,38 @@ class FlatAdamTrainer:
             self._launch_bucket(self._next_bucket)
             self._next_bucket += 1
 
-    def capture(self, batch: dict, optimizer_in_graph: bool = True) -> None:
+    def capture(self, batch: dict, optimizer_in_graph: bool = True, micro_batches: int = 1) -> None:
         """Record one WHOLE optimisation step into a CUDA graph: zero the flat gradient, forward, loss, backward, the
         gradient all-reduce (world > 1: one NCCL all-reduce per bucket, forked onto NCCL's stream as soon as the
         bucket's last weight-gradient kernel has been recorded, joined before Adam) and the Adam update (step index
         kept on the device, ``npfk_adam_step_dev``).  Static copies of ``batch``'s tensors are made; every later batch
         must have the same shapes.  Call after at least two eager ``step`` calls (buffers laid out in readiness order,
         kernels' one-time host initialisation done).  ``optimizer_in_graph=False`` keeps the round-1 behaviour (one
-        blocking all-reduce and an eager Adam launch after every replay)."""
+        blocking all-reduce and an eager Adam launch after every replay).
+
+        ``micro_batches > 1`` (gradient accumulation, e.g. BASELINE.json configs[3]: a fixed global batch of 128 tasks at
+        1/2/4/8 GPUs): three more graphs are recorded -- first (zero + forward/backward), middle (forward/backward into
+        the same flat gradient) and last (forward/backward + all-reduce + Adam with the gradient scaled by
+        1 / (world * micro_batches)) -- and ``step_graphed(batch, first=, last=)`` replays the matching one."""
         assert self._order is not None, "run eager steps before capture()"
         torch.cuda.synchronize()
         self._static = {k: v.clone() for k, v in batch.items()}
         self._opt_in_graph = bool(optimizer_in_graph) and self.adam_impl is K.adam_step
+        self._micro = max(1, int(micro_batches))
         if getattr(self, "_step_dev", None) is None:      # ONE device-side step counter shared by every captured graph
             self._step_dev = torch.zeros(1, dtype=torch.int32, device=self.flat_param.device)
         self._step_dev.fill_(self.step_count)
         if self._opt_in_graph and self.world > 1:
             self._rehearse()
             torch.cuda.synchronize()
-        self._capturing = True
-        self._graph = torch.cuda.CUDAGraph()
-        # weight-gradient kernels add straight into the flat gradient buffer (NPFK_DIRECT_GRAD=0: through autograd)
-        K.set_direct_grad(os.environ.get("NPFK_DIRECT_GRAD", "1") != "0")
-        self._pending.clear()
-        self._event_no, self._next_bucket = 0, 0
-        fork = self._opt_in_graph and self.world > 1
-        if fork:
-            self._event_cb = self._capture_event
-            K.set_sink_callback(self._capture_event)
-        try:
-            with torch.cuda.graph(self._graph):
-                self.flat_grad.zero_()
-                if K.get_mode() == K.MODE_FAST:       # one rounding kernel for every weight of the step
-                    K.set_tf32_flat(self.flat_param)
-                out = self.model(**self._static)
-                loss = self.criterion(out, self._static["Y_trgt"])
-                loss.backward()
-                self._static_loss = loss.detach()
-                if self._opt_in_graph:
-                    if fork:
-                        assert self._event_no == self._n_events, "the captured step differs from its rehearsal"
-                        while self._next_bucket < len(self.bucket_slices):
-                            self._launch_bucket(self._next_bucket)
-                            self._next_bucket += 1
-                        for w in self._pending:
-                            w.wait()
-                    K.adam_step_dev(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr,
-                                    self.betas[0], self.betas[1], self.eps, self._step_dev, 1.0 / self.world)
-        finally:
-            self._capturing = False
-            self._event_cb = None
-            self._pending.clear()
-            K.set_direct_grad(False)
-            K.set_sink_callback(None)
-            K.set_tf32_flat(None)
+        self._losses = {}
+        self._graphs = {(True, True): self._capture_variant(True, True)}
+        if self._micro > 1:
+            assert self._opt_in_graph, "gradient accumulation over micro-batches needs the optimiser inside the graph"
+            for key in ((True, False), (False, False), (False, True)):
+                self._graphs[key] = self._capture_variant(*key)
+        self._graph = self._graphs[(True, True)]
+        self._static_loss = self._losses[(True, True)]
         for p_idx, p in enumerate(self.params):
             o, n = self.offsets[p_idx]
             assert p.grad is not None and p.grad.data_ptr() == self.flat_grad.data_ptr() + 4 * o, \
@@ -264,6 +242,52 @@ class FlatAdamTrainer:
             self.model._pending_flag = None
             self._flag_host = torch.zeros(1, dtype=self._flag_dev.dtype).pin_memory()
             self._flag_event = None
+
+    def _capture_variant(self, zero: bool, update: bool):
+        """one CUDA graph of [zero the flat gradient] + forward + loss + backward [+ all-reduce + Adam]"""
+        graph = torch.cuda.CUDAGraph()
+        if getattr(self, "_pool", None) is None:          # the variants never run concurrently: one memory pool
+            self._pool = torch.cuda.graph_pool_handle()
+        self._capturing = True
+        # weight-gradient kernels add straight into the flat gradient buffer (NPFK_DIRECT_GRAD=0: through autograd)
+        K.set_direct_grad(os.environ.get("NPFK_DIRECT_GRAD", "1") != "0")
+        self._pending.clear()
+        self._event_no, self._next_bucket = 0, 0
+        opt = self._opt_in_graph and update
+        fork = opt and self.world > 1
+        if fork:
+            self._event_cb = self._capture_event
+            K.set_sink_callback(self._capture_event)
+        scale = 1.0 / (self.world * (self._micro if not (zero and update) else 1))
+        try:
+            with torch.cuda.graph(graph, pool=self._pool):
+                if zero:
+                    self.flat_grad.zero_()
+                if K.get_mode() == K.MODE_FAST:       # one rounding kernel for every weight of the step
+                    K.set_tf32_flat(self.flat_param)
+                out = self.model(**self._static)
+                loss = self.criterion(out, self._static["Y_trgt"])
+                loss.backward()
+                static_loss = loss.detach()
+                if opt:
+                    if fork:
+                        assert self._event_no == self._n_events, "the captured step differs from its rehearsal"
+                        while self._next_bucket < len(self.bucket_slices):
+                            self._launch_bucket(self._next_bucket)
+                            self._next_bucket += 1
+                        for w in self._pending:
+                            w.wait()
+                    K.adam_step_dev(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr,
+                                    self.betas[0], self.betas[1], self.eps, self._step_dev, scale)
+        finally:
+            self._capturing = False
+            self._event_cb = None
+            self._pending.clear()
+            K.set_direct_grad(False)
+            K.set_sink_callback(None)
+            K.set_tf32_flat(None)
+        self._losses[(zero, update)] = static_loss
+        return graph
 
     def prefetch(self, batch: dict) -> None:
         """Start the H2D copy of the NEXT step's batch (pinned host tensors) on a side stream into a device staging
@@ -283,8 +307,9 @@ class FlatAdamTrainer:
             self._stage_ready.record()
         self._stage_src = batch
 
-    def step_graphed(self, batch: dict) -> torch.Tensor:
-        """One optimisation step replaying the captured graph (forward, loss, backward, bucketed all-reduce, Adam) after
+    def step_graphed(self, batch: dict, first: bool = True, last: bool = True) -> torch.Tensor:
+        """``first`` / ``last``: position of this micro-batch in the optimisation step (``capture(micro_batches=n)``);
+        the default is a whole step.  One optimisation step replaying the captured graph (forward, loss, backward, bucketed all-reduce, Adam) after
         the H2D/D2D copy of the batch into the static buffers.  Returns the graph's static loss tensor: it is
         OVERWRITTEN by the next replay, so read or clone it before the next call.  The [-1,1] range check of the reference (base.py:241-247) is
         read back asynchronously and raised at most one step late."""
@@ -302,7 +327,10 @@ class FlatAdamTrainer:
             for k, v in batch.items():
                 if v is not self._static[k]:
                     self._static[k].copy_(v, non_blocking=True)
-        self._graph.replay()
+        key = (bool(first), bool(last))
+        self._graphs[key].replay()
+        if not last:
+            return self._losses[key]
         if self._flag_dev is not None and self._flag_event is None:
             self._flag_host.copy_(self._flag_dev, non_blocking=True)
             self._flag_event = torch.cuda.Event()
@@ -314,7 +342,7 @@ class FlatAdamTrainer:
             self.adam_impl(self.flat_param, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0],
                            self.betas[1], self.eps, self.step_count, 1.0 / self.world)
         K.tf32_cache_clear()      # the weights changed without bumping tensor versions
-        return self._static_loss
+        return self._losses[key]
 
     def _gather_state(self, flat):
         return {i: flat[o:o + n].clone() for i, (o, n) in self.offsets.items()}

@@ -215,3 +215,42 @@ def test_full_size_properties_convcnp_unet():
     assert torch.isfinite(a).all()
     assert rel_err(b, a[:, :1]) < 1e-5       # eval BatchNorm: tasks do not interact
     assert torch.equal(a, c)
+
+
+@pytest.mark.parametrize("name", ["AttnCNP", "ConvCNP_unet", "AttnLNP"])
+def test_predict_sharded_matches_one_pass(name):
+    """configs[4] driver: the shards of W ranks, chunked and double-buffered from pinned host memory, reproduce the
+    summaries of one forward over all tasks (replicas only, nothing exchanged)"""
+    from npf_gwwaveform_b200.utils.predict import default_summary, predict_sharded
+
+    torch.manual_seed(0)
+    m = build_product(name, 128, nz=4).cuda().eval()
+    n, Nc, Nt = 13, 40, 300
+    tasks = {k: v.pin_memory() for k, v in chirp_batch(n, Nc, Nt, 77).items()}
+    if "LNP" in name:
+        eps = torch.randn(4, n, 1, 128, generator=torch.Generator().manual_seed(3)).cuda()
+        state = {"lo": 0}
+        m.draw_eps = lambda nz, like: eps[:, state["lo"]:state["lo"] + like.shape[0]]
+    with torch.no_grad():
+        dev = {k: v.cuda() for k, v in tasks.items()}
+        whole = default_summary(m(dev["X_cntxt"], dev["Y_cntxt"], dev["X_trgt"])[0], dev)
+    got = torch.full_like(whole, float("nan"))
+    covered = 0
+    for rank in range(3):
+        if "LNP" in name:       # the injected noise has to follow the shard / chunk offsets
+            from npf_gwwaveform_b200.training import shard_range
+
+            lo, hi = shard_range(n, rank, 3)
+            outs = []
+            for s in range(lo, hi, 2):
+                state["lo"] = s
+                o, _ = predict_sharded(m, {k: v[s:min(hi, s + 2)] for k, v in tasks.items()}, chunk=2, rank=0, world_size=1)
+                outs.append(o)
+            out = torch.cat(outs) if outs else whole[:0]
+        else:
+            out, (lo, hi) = predict_sharded(m, tasks, chunk=2, rank=rank, world_size=3)
+        assert out.shape == (hi - lo, whole.shape[1])
+        got[lo:hi] = out
+        covered += hi - lo
+    assert covered == n and not torch.isnan(got).any()
+    assert rel_err(got, whole) < 1e-4
