@@ -10,6 +10,7 @@ global batch is 256*N, sharded over ranks; the only exchange is the gradient all
 forward + CNPFLoss + backward + all-reduce + Adam.  Prints ONE JSON line on rank 0.
 """
 import argparse
+import datetime
 import json
 import os
 import statistics
@@ -581,6 +582,10 @@ def dp_check(res, dev, rank, world):
         crit(model(**batch), batch["Y_trgt"]).backward()
         return trainer.flat_grad.clone()
 
+    # the trainer's post-accumulate hooks would launch bucket all-reduces from inside these backward passes (and rank 0
+    # runs more of them than the other ranks): route the hook events to a no-op for the duration of the check
+    trainer._event_cb = lambda _i: None
+
     g_local = grad_of(shard)
     g_dp = g_local.clone()
     dist.all_reduce(g_dp, op=dist.ReduceOp.SUM)
@@ -595,6 +600,7 @@ def dp_check(res, dev, rank, world):
             g_ref += grad_of({k: gathered[k][r] for k in shard})
         g_ref /= world
         out = float((g_dp - g_ref).norm() / g_ref.norm().clamp_min(1e-30))
+    trainer._event_cb = None
     trainer.flat_grad.zero_()
     with torch.no_grad():
         for n, b in model.named_buffers():
@@ -620,7 +626,8 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # NCCL prints its version banner (NCCL_DEBUG=VERSION/WARN/INFO) on stdout: keep stdout to the ONE JSON line
         os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/npf_nccl_%h_%p.log")
-        dist.init_process_group("nccl", device_id=dev)
+        # a mismatched collective must fail fast, not sit in NCCL's default 10-minute watchdog window
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     npf.set_mode(args.mode)
     set_lazy_validation(True)                       # range flag still computed every step, read one step late
 
