@@ -5,7 +5,7 @@ CUDA kernels of ``libnpfk.so`` (C-ABI in include/npfk.h).  There is no CPU fallb
 """
 from . import kernels
 from .architectures import *  # noqa: F401,F403
-from .kernels import get_mode, launch_count, set_mode
+from .kernels import get_mode, launch_count, set_mode, set_sync_bn
 from .losses import *  # noqa: F401,F403
 from .neuralproc import *  # noqa: F401,F403
 

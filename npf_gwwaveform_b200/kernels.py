@@ -158,7 +158,8 @@ def tf32_weight(w: torch.Tensor) -> torch.Tensor:
     if not wv.is_contiguous():
         wv = wv.contiguous()
     capturing = torch.cuda.is_current_stream_capturing()
-    key = (id(base), w.storage_offset(), tuple(w.shape), tuple(w.stride()))
+    # data_ptr / device in the key: `p.data = ...` or module.to() re-point a parameter without bumping its version
+    key = (id(base), w.data_ptr(), str(w.device), w.storage_offset(), tuple(w.shape), tuple(w.stride()))
     if not capturing:
         hit = _tf32_cache.get(key)
         if hit is not None and hit[0]() is base and hit[1] == base._version:
@@ -783,6 +784,25 @@ def setconv_interp(xk, xq, v, theta, wd, bias=None, p=2.0, unshared=False):
 
 
 # ------------------------------------------------------------------------------------------ conv blocks
+def set_sync_bn(flag: bool, group=None) -> None:
+    """``sync_bn`` option of SURVEY.md section 8e: in training mode the BatchNorm layers of the conv blocks all-reduce
+    their per-channel (sum x, sum x^2, count) over ``group`` (default: the world) in forward and (sum dh, sum dh*xhat) in
+    backward, so that data-parallel training normalises with the statistics of the GLOBAL batch, as the reference does
+    when it sees that batch on one device (npf/architectures/cnn.py:189,193).  Off by default: per-replica statistics."""
+    _state["sync_bn"] = (bool(flag), group)
+
+
+def _sync_bn_group():
+    flag, group = _state.get("sync_bn", (False, None))
+    if not flag:
+        return None
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 2:
+        return None
+    return (group,)          # a 1-tuple: `group` itself may be None (= the default group)
+
+
 class _NormActDwConvFn(Function):
     """y = dwconv(act(norm(x))) + bias + res on channel-last [B,L,C]; BatchNorm statistics handled inside."""
 
@@ -800,7 +820,33 @@ class _NormActDwConvFn(Function):
         mean = var = None
         if has_norm:
             gamma, beta = _c(gamma), _c(beta)
-            if training:
+            sync = _sync_bn_group() if training else None
+            ctx.sync = None
+            if training and sync is not None:
+                import torch.distributed as dist
+
+                # local statistics (no running-stat update), then one all-reduce of [sum x | sum x^2 | count]
+                stats = torch.empty(2 * C, device=x.device, dtype=torch.float32)
+                scratch = torch.empty(2 * C, device=x.device, dtype=torch.float64)
+                LIB.call("npfk_bn_stats", _p(x), B * L, C, _p(scratch), _p(stats), None, None, 0.0, None, st)
+                n_loc = float(B * L)
+                m_l, v_l = stats[:C].double(), stats[C:].double()
+                pack = torch.cat([m_l * n_loc, (v_l + m_l * m_l) * n_loc, torch.full((1,), n_loc, device=x.device,
+                                                                                    dtype=torch.float64)])
+                dist.all_reduce(pack, group=sync[0])
+                n_tot = pack[-1]
+                m_g = pack[:C] / n_tot
+                v_g = (pack[C:2 * C] / n_tot - m_g * m_g).clamp_min(0.0)
+                mean, var = m_g.float(), v_g.float()
+                with torch.no_grad():
+                    if running_mean is not None:
+                        running_mean.mul_(1.0 - momentum).add_(mean, alpha=momentum)
+                        running_var.mul_(1.0 - momentum).add_((v_g * (n_tot / (n_tot - 1.0).clamp_min(1.0))).float(),
+                                                               alpha=momentum)
+                    if num_batches_tracked is not None:
+                        num_batches_tracked.add_(1)
+                ctx.sync = (sync[0], n_loc, n_tot.float())
+            elif training:
                 stats = torch.empty(2 * C, device=x.device, dtype=torch.float32)
                 scratch = torch.empty(2 * C, device=x.device, dtype=torch.float64)
                 LIB.call("npfk_bn_stats", _p(x), B * L, C, _p(scratch), _p(stats), _p(running_mean), _p(running_var),
@@ -842,8 +888,25 @@ class _NormActDwConvFn(Function):
         if has_norm:
             dgamma = sinks[0] if sinks[0] is not None else z[C * (ks + 3):C * (ks + 4)]
             dbeta = sinks[1] if sinks[1] is not None else z[C * (ks + 4):]
-            LIB.call("npfk_bn_bwd", _p(dh), _p(x), _p(mean), _p(var), _p(gamma), eps, _p(sums), _p(dx), _p(dgamma),
-                     _p(dbeta), B * L, C, int(training), st)
+            if getattr(ctx, "sync", None) is not None:
+                import torch.distributed as dist
+
+                # dx needs the GLOBAL sums (sum dh, sum dh*xhat) / N_total; gamma / beta take this rank's sums (the
+                # gradient all-reduce adds the ranks up).  npfk_bn_bwd divides by the local row count, so the global
+                # sums are pre-scaled by n_local / N_total; its "+=" of the sums goes to a scratch pair
+                group, n_loc, n_tot = ctx.sync
+                local = sums.clone()
+                glob = sums.clone()
+                dist.all_reduce(glob, group=group)
+                glob.mul_(n_loc / n_tot)
+                junk = torch.empty(2 * C, device=dev, dtype=torch.float32)
+                LIB.call("npfk_bn_bwd", _p(dh), _p(x), _p(mean), _p(var), _p(gamma), eps, _p(glob), _p(dx), _p(junk[:C]),
+                         _p(junk[C:]), B * L, C, int(training), st)
+                dbeta.add_(local[:C])
+                dgamma.add_(local[C:])
+            else:
+                LIB.call("npfk_bn_bwd", _p(dh), _p(x), _p(mean), _p(var), _p(gamma), eps, _p(sums), _p(dx), _p(dgamma),
+                         _p(dbeta), B * L, C, int(training), st)
         if has_norm:
             dgamma, dbeta = (None if sinks[0] is not None else dgamma), (None if sinks[1] is not None else dbeta)
         dw = None if sinks[2] is not None else dw.reshape(wshape)

@@ -243,6 +243,19 @@ class FlatAdamTrainer:
             self._flag_host = torch.zeros(1, dtype=self._flag_dev.dtype).pin_memory()
             self._flag_event = None
 
+    _CAPTURE_FIELDS = ("_graphs", "_losses", "_graph", "_static", "_static_loss", "_flag_dev", "_flag_host", "_flag_event",
+                       "_micro", "_opt_in_graph", "_stage", "_stage_src")
+
+    def export_capture(self) -> dict:
+        """the state ``capture`` created (graphs, their static inputs / loss tensors, range-flag plumbing), so that a
+        caller can keep one capture per input shape and switch between them with ``import_capture``"""
+        return {k: getattr(self, k, None) for k in self._CAPTURE_FIELDS}
+
+    def import_capture(self, state: dict) -> None:
+        for k in self._CAPTURE_FIELDS:
+            setattr(self, k, state.get(k))
+        self._flag_event = None
+
     def _capture_variant(self, zero: bool, update: bool):
         """one CUDA graph of [zero the flat gradient] + forward + loss + backward [+ all-reduce + Adam]"""
         graph = torch.cuda.CUDAGraph()

@@ -130,6 +130,10 @@ class CntxtTrgtGetter:
     def __call__(self, X, y=None, context_indcs=None, target_indcs=None, is_return_indcs=False):
         K.require_cuda(X, y)
         batch_size, num_points = self.getter_inputs(X)
+        # indices handed in by the caller are checked synchronously (IndexError here, as torch.gather in the reference);
+        # indices drawn by the getters on the device are checked without a host synchronisation (raised one call late)
+        check_c = "sync" if context_indcs is not None else "async"
+        check_t = "sync" if target_indcs is not None else "async"
         if context_indcs is None:
             context_indcs = self.contexts_getter(batch_size, num_points, device=X.device)
         all_targets = target_indcs is None and self.targets_getter is get_all_indcs and not self.is_add_cntxts_to_trgts
@@ -140,11 +144,11 @@ class CntxtTrgtGetter:
         X_pre_cntxt = self.preprocess_context(X)
         if is_return_indcs:
             return context_indcs, X_pre_cntxt, target_indcs, X
-        X_cntxt, Y_cntxt = self.select(X_pre_cntxt, y, context_indcs)
+        X_cntxt, Y_cntxt = self.select(X_pre_cntxt, y, context_indcs, check=check_c)
         if all_targets:        # every point is a target: the gather would be an identity copy of two tensors
             X_trgt, Y_trgt = X, y
         else:
-            X_trgt, Y_trgt = self.select(X, y, target_indcs)
+            X_trgt, Y_trgt = self.select(X, y, target_indcs, check=check_t)
         return X_cntxt, Y_cntxt, X_trgt, Y_trgt
 
     def preprocess_context(self, X):
@@ -158,12 +162,30 @@ class CntxtTrgtGetter:
         batch_size, num_points, _ = X.shape
         return batch_size, num_points
 
-    def select(self, X, y, indcs):
-        """(X[b, indcs[b]], y[b, indcs[b]]) as fresh contiguous tensors; an index outside [0, N) raises IndexError."""
-        return _gather(X, indcs), _gather(y, indcs)
+    def select(self, X, y, indcs, check="sync"):
+        """(X[b, indcs[b]], y[b, indcs[b]]) as fresh contiguous tensors; an index outside [0, N) raises IndexError
+        (``check``: see ``_gather``; out-of-range rows are written as zeros, never read out of bounds)."""
+        return _gather(X, indcs, check), _gather(y, indcs, check)
 
 
-def _gather(src, indcs):
+_pending_bad = []      # (event, pinned host flag, N) of gathers whose out-of-range flag has not been looked at yet
+
+
+def _poll_bad(block: bool = False):
+    """raise IndexError for an earlier gather whose index flag has arrived (never waits unless ``block``)"""
+    while _pending_bad and (block or _pending_bad[0][0].query()):
+        ev, host, N = _pending_bad.pop(0)
+        if block:
+            ev.synchronize()
+        if int(host.item()):
+            _pending_bad.clear()
+            raise IndexError(f"select: index out of range for {N} points (detected on an earlier gather)")
+
+
+def _gather(src, indcs, check: str = "async"):
+    """``check``: "async" (default) copies the kernel's out-of-range flag to pinned host memory without waiting and
+    raises from a LATER call once it has arrived (no host synchronisation on the training path; the kernel clamps, so
+    nothing is read out of bounds); "sync" waits and raises here, as the reference's torch.gather would."""
     K.require_cuda(src)
     B, N, D = src.shape
     src = src.contiguous().float()
@@ -175,8 +197,19 @@ def _gather(src, indcs):
     bad = torch.zeros(1, dtype=torch.int32, device=src.device)
     LIB.call("npfk_gather_rows", src.data_ptr(), indcs.data_ptr(), dst.data_ptr(), B, N, n, D, bad.data_ptr(),
              torch.cuda.current_stream().cuda_stream)
-    if not torch.cuda.is_current_stream_capturing() and n > 0 and int(bad.item()):
-        raise IndexError(f"select: index out of range for {N} points")
+    if not torch.cuda.is_current_stream_capturing() and n > 0:
+        if check == "sync":
+            if int(bad.item()):
+                raise IndexError(f"select: index out of range for {N} points")
+        else:
+            _poll_bad()
+            host = torch.empty(1, dtype=torch.int32).pin_memory()
+            host.copy_(bad, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            _pending_bad.append((ev, host, N))
+            if len(_pending_bad) > 64:
+                _poll_bad(block=True)
     return dst
 
 

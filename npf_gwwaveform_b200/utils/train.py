@@ -59,6 +59,9 @@ class NeuralNetShim:
         self.valid_batch_size = iterator_valid__batch_size or 2 * batch_size
         self.decay_lr, self.seed, self.use_cuda_graph, self.verbose = decay_lr, seed, use_cuda_graph, verbose
         self.history = []
+        # captures kept at once (the default collate draws 51 context sizes: every one gets its graph, they share one
+        # memory pool; least recently used is dropped beyond this)
+        self.max_graphs = 64
         self.initialized_ = False
 
     # ------------------------------------------------------------------ skorch surface
@@ -94,20 +97,17 @@ class NeuralNetShim:
         self.module_.train()
         shapes = tuple((k, tuple(v.shape)) for k, v in sorted(Xi.items()))
         if self.use_cuda_graph and self.trainer_._order is not None and self.trainer_.step_count >= 2:
-            if self._graph_shapes != shapes:       # the context size changes from batch to batch: one graph per shape
+            if self._graph_shapes != shapes:       # the context size changes from batch to batch: one capture per shape
                 self._graphs = getattr(self, "_graphs", {})
-                if shapes not in self._graphs and len(self._graphs) < 8:
+                if shapes not in self._graphs:
+                    if len(self._graphs) >= self.max_graphs:            # least recently used capture makes room
+                        self._graphs.pop(next(iter(self._graphs)))
                     self.trainer_.capture(Xi)
-                    self._graphs[shapes] = (self.trainer_._graph, self.trainer_._static, self.trainer_._static_loss,
-                                            self.trainer_._flag_dev, getattr(self.trainer_, "_flag_host", None))
-                if shapes in self._graphs:
-                    (self.trainer_._graph, self.trainer_._static, self.trainer_._static_loss, self.trainer_._flag_dev,
-                     fh) = self._graphs[shapes]
-                    if fh is not None:
-                        self.trainer_._flag_host, self.trainer_._flag_event = fh, None
-                    self._graph_shapes = shapes
+                    self._graphs[shapes] = self.trainer_.export_capture()
                 else:
-                    self._graph_shapes = None
+                    self._graphs[shapes] = self._graphs.pop(shapes)     # move to the most-recent end
+                    self.trainer_.import_capture(self._graphs[shapes])
+                self._graph_shapes = shapes
             if self._graph_shapes == shapes:
                 return {"loss": self.trainer_.step_graphed(Xi).clone()}     # the graph's loss tensor is reused
         return {"loss": self.trainer_.step(Xi)}
@@ -293,7 +293,16 @@ def train_models(datasets, models, criterion, test_datasets=dict(), valid_datase
                 print(suffix, "| epochs:", len(trainer.history), "| train loss:",
                       None if not trainer.history else round(trainer.history[-1]["train_loss"], 4),
                       "| test log likelihood:", None if test_loglike is None else round(test_loglike, 4), flush=True)
+                # the reference hands back CPU modules (utils/train.py:335-338).  Moving the module re-creates every
+                # parameter's storage, so the flat Adam buffers and the captured graphs no longer alias the weights: drop
+                # them; a later fit() / initialize() rebuilds the trainer on whatever device the module is moved to
                 trainer.module_.cpu()
+                if getattr(trainer, "trainer_", None) is not None:
+                    trainer.trainer_.close()
+                trainer.trainer_ = None
+                trainer._graphs, trainer._graph_shapes = {}, None
+                trainer.initialized_ = False
+                trainer.module = trainer.module_
                 torch.cuda.empty_cache()
                 trainers[suffix] = trainer
     return trainers
