@@ -15,6 +15,7 @@
 // CTA, and inside a visited chunk only keys with a non-negligible weight for some query reach the value phase.
 // No assumption is made on key order: unsorted keys only make the skip test succeed less often.
 #include <math_constants.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -473,6 +474,183 @@ setconv_interp_bwd_kernel(const InterpArgs a, const float* __restrict__ stats, c
     }
 }
 
+
+// ------------------------------------------------------------------------------------------ forward, resident values
+// Grid -> target interpolation when one task's value rows fit in shared memory (C == 128, Nk <= 256: the ConvCNP case,
+// 192 induced points).  The write of 512 B per target is the only large HBM stream, so the kernel is organised around
+// it: a CTA stages the task's [Nk, 128] values once (L2 hits after the first CTA of a task), then each warp takes 32
+// queries.
+//   phase 1 (lane = query): nearest key by bisection when the keys are sorted (they are a linspace for ConvCNP; the
+//     sortedness is checked on the device), the window of keys whose weight is not negligible (the same 2^-40 / e^-46
+//     cut-offs as the tiled kernel above), un-normalised weights of the warp's window into a [slot][query] table;
+//   phase 2 (lane = 4 channels): out[q, :] = sum_slot w[slot][q] * V[key(slot), :] with 16 queries accumulated in
+//     registers per pass, so a value row is read from shared memory once per 16 queries, and one 512-byte streaming store
+//     per target row.
+// Unsorted keys take the same code with the window [0, Nk); a window wider than kV2Slots is processed in rounds.
+constexpr int kV2Threads = 512;
+constexpr int kV2Slots = 32;
+constexpr int kV2MaxKeys = 256;
+
+__global__ void __launch_bounds__(kV2Threads, 1)
+setconv_interp_fwd_v2_kernel(const InterpArgs a, float* __restrict__ out, float* __restrict__ stats) {
+    extern __shared__ __align__(16) float smem_v2[];
+    float* sV = smem_v2;                                   // [Nk][128]
+    float* sKeys = sV + (size_t)a.Nk * 128;                // [Nk]
+    float* sWq = sKeys + kV2MaxKeys;                       // [16 warps][kV2Slots][32]
+    float* sQ = sWq + 16 * kV2Slots * 32;                  // [16 warps][2][32]: 1 / normaliser, density
+    const int b = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int Nk = (int)a.Nk;
+    const float* xkb = a.xk + (int64_t)b * a.sxk;
+    {
+        const float4* src = reinterpret_cast<const float4*>(a.v + (int64_t)b * a.Nk * 128);
+        float4* dst = reinterpret_cast<float4*>(sV);
+        for (int i = threadIdx.x; i < Nk * 32; i += kV2Threads) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < Nk; i += kV2Threads) sKeys[i] = __ldg(xkb + i);
+    }
+    __syncthreads();
+    bool ok = true;
+    for (int i = threadIdx.x; i + 1 < Nk; i += kV2Threads) ok = ok && (sKeys[i] <= sKeys[i + 1]);
+    const bool sorted = __syncthreads_and(ok) != 0;
+
+    const float sigma = 1e-5f + softplus_f(__ldg(a.theta));
+    const float sigma_d = a.unshared ? 1e-5f + softplus_f(__ldg(a.theta + 1)) : sigma;
+    const int64_t q0 = (int64_t)blockIdx.x * (kV2Threads) + warp * 32;      // 32 queries per warp, 512 per CTA
+    if (q0 >= a.Nq) return;
+    const int nq = (int)min((int64_t)32, a.Nq - q0);
+    const bool qv = lane < nq;
+    const float xq = qv ? __ldg(a.xq + (int64_t)b * a.sxq + q0 + lane) : sKeys[0];
+    float* wq = sWq + warp * kV2Slots * 32;
+    float* sq = sQ + warp * 64;
+
+    // ---- phase 1: stabiliser (inp at the nearest key) and the window of keys that matter for this query
+    float m = 0.f;
+    int kl = 0, kr = Nk - 1;
+    if (sorted) {
+        int lo = 0, hi = Nk;                    // first key >= xq
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (sKeys[mid] < xq) lo = mid + 1; else hi = mid;
+        }
+        int near = lo < Nk ? lo : Nk - 1;
+        if (lo > 0 && (lo >= Nk || fabsf(sKeys[lo - 1] - xq) <= fabsf(sKeys[lo] - xq))) near = lo - 1;
+        const float dmin = fabsf(sKeys[near] - xq);
+        if (!a.unshared) m = interp_inp_d(dmin, sigma, a.p);
+        kl = kr = near;
+        if (a.unshared) {
+            while (kl > 0 && fmaxf(interp_inp_d(fabsf(sKeys[kl - 1] - xq), sigma, a.p),
+                                   interp_inp_d(fabsf(sKeys[kl - 1] - xq), sigma_d, a.p)) > kCutUnshared) --kl;
+            while (kr < Nk - 1 && fmaxf(interp_inp_d(fabsf(sKeys[kr + 1] - xq), sigma, a.p),
+                                        interp_inp_d(fabsf(sKeys[kr + 1] - xq), sigma_d, a.p)) > kCutUnshared) ++kr;
+        } else {
+            while (kl > 0 && interp_inp_d(fabsf(sKeys[kl - 1] - xq), sigma, a.p) - m > kCutShared) --kl;
+            while (kr < Nk - 1 && interp_inp_d(fabsf(sKeys[kr + 1] - xq), sigma, a.p) - m > kCutShared) ++kr;
+        }
+    } else if (!a.unshared) {
+        float dmin = CUDART_INF_F;
+        for (int k = 0; k < Nk; ++k) dmin = fminf(dmin, fabsf(sKeys[k] - xq));
+        m = interp_inp_d(dmin, sigma, a.p);
+    }
+    // the warp's window: union over its queries
+    int wl = kl, wr = kr;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        wl = min(wl, __shfl_xor_sync(0xffffffffu, wl, o));
+        wr = max(wr, __shfl_xor_sync(0xffffffffu, wr, o));
+    }
+    const bool single = (wr - wl + 1) <= kV2Slots;
+    float l = 0.f;
+    // weights of window slice [k0, k0 + kV2Slots) into the table; `sum` adds them to the normaliser
+    auto fill = [&](int k0, bool sum) {
+        __syncwarp();
+#pragma unroll 4
+        for (int sidx = 0; sidx < kV2Slots; ++sidx) {
+            const int k = k0 + sidx;
+            float e = 0.f;
+            if (k <= wr) {
+                const float d = fabsf(sKeys[k] - xq);
+                if (a.unshared) {
+                    e = expf(interp_inp_d(d, sigma, a.p));
+                    if (sum) l += expf(interp_inp_d(d, sigma_d, a.p));
+                } else {
+                    e = expf(interp_inp_d(d, sigma, a.p) - m);
+                    if (sum) l += e;
+                }
+            }
+            wq[sidx * 32 + lane] = e;
+        }
+        __syncwarp();
+    };
+    if (single) {
+        fill(wl, true);
+    } else {
+        for (int k = wl; k <= wr; ++k) {          // normaliser over the whole window first
+            const float d = fabsf(sKeys[k] - xq);
+            l += a.unshared ? expf(interp_inp_d(d, sigma_d, a.p)) : expf(interp_inp_d(d, sigma, a.p) - m);
+        }
+    }
+    {
+        float density, inv;
+        if (a.unshared) {
+            density = l;
+            inv = 1.f / (l + 1e-8f);
+        } else {
+            density = l * expf(m);
+            inv = 1.f / l;
+        }
+        sq[lane] = inv;
+        sq[32 + lane] = density;
+        if (qv) *reinterpret_cast<float2*>(stats + ((int64_t)b * a.Nq + q0 + lane) * 2) = make_float2(density, l);
+    }
+    __syncwarp();
+
+    // ---- phase 2: lane = channels 4 lane .. 4 lane + 3
+    const float4 wd4 = __ldg(reinterpret_cast<const float4*>(a.wd) + lane);
+    const float4 b4 = a.bias ? __ldg(reinterpret_cast<const float4*>(a.bias) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* v4 = reinterpret_cast<const float4*>(sV) + lane;
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {
+        if (h * 16 >= nq) break;
+        float4 acc[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k0 = wl; k0 <= wr; k0 += kV2Slots) {
+            if (!single) fill(k0, false);
+            const int ns = min(kV2Slots, wr - k0 + 1);
+#pragma unroll 2
+            for (int sidx = 0; sidx < ns; ++sidx) {
+                const float4 vv = v4[(size_t)(k0 + sidx) * 32];
+                const float4* w4 = reinterpret_cast<const float4*>(wq + sidx * 32 + h * 16);
+#pragma unroll
+                for (int i4 = 0; i4 < 4; ++i4) {
+                    const float4 w = w4[i4];
+                    acc[4 * i4].x = fmaf(w.x, vv.x, acc[4 * i4].x); acc[4 * i4].y = fmaf(w.x, vv.y, acc[4 * i4].y);
+                    acc[4 * i4].z = fmaf(w.x, vv.z, acc[4 * i4].z); acc[4 * i4].w = fmaf(w.x, vv.w, acc[4 * i4].w);
+                    acc[4 * i4 + 1].x = fmaf(w.y, vv.x, acc[4 * i4 + 1].x); acc[4 * i4 + 1].y = fmaf(w.y, vv.y, acc[4 * i4 + 1].y);
+                    acc[4 * i4 + 1].z = fmaf(w.y, vv.z, acc[4 * i4 + 1].z); acc[4 * i4 + 1].w = fmaf(w.y, vv.w, acc[4 * i4 + 1].w);
+                    acc[4 * i4 + 2].x = fmaf(w.z, vv.x, acc[4 * i4 + 2].x); acc[4 * i4 + 2].y = fmaf(w.z, vv.y, acc[4 * i4 + 2].y);
+                    acc[4 * i4 + 2].z = fmaf(w.z, vv.z, acc[4 * i4 + 2].z); acc[4 * i4 + 2].w = fmaf(w.z, vv.w, acc[4 * i4 + 2].w);
+                    acc[4 * i4 + 3].x = fmaf(w.w, vv.x, acc[4 * i4 + 3].x); acc[4 * i4 + 3].y = fmaf(w.w, vv.y, acc[4 * i4 + 3].y);
+                    acc[4 * i4 + 3].z = fmaf(w.w, vv.z, acc[4 * i4 + 3].z); acc[4 * i4 + 3].w = fmaf(w.w, vv.w, acc[4 * i4 + 3].w);
+                }
+            }
+        }
+        float* op = out + ((int64_t)b * a.Nq + q0 + h * 16) * 128 + 4 * lane;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if (h * 16 + i < nq) {
+                const float inv = sq[h * 16 + i], dens = sq[32 + h * 16 + i];
+                float4 o;
+                o.x = fmaf(acc[i].x, inv, fmaf(dens, wd4.x, b4.x));
+                o.y = fmaf(acc[i].y, inv, fmaf(dens, wd4.y, b4.y));
+                o.z = fmaf(acc[i].z, inv, fmaf(dens, wd4.z, b4.z));
+                o.w = fmaf(acc[i].w, inv, fmaf(dens, wd4.w, b4.w));
+                __stcs(reinterpret_cast<float4*>(op + (int64_t)i * 128), o);
+            }
+        }
+    }
+}
+
 }  // namespace npfk
 
 using namespace npfk;
@@ -487,6 +665,30 @@ int npfk_setconv_interp_fwd(const float* xk, int64_t sxk, const float* xq, int64
                  B, (long long)Nk, (long long)Nq, C);
     NPFK_REQUIRE(p > 0.f, "setconv_interp_fwd: p must be positive");
     InterpArgs a{xk, sxk, xq, sxq, v, theta, wd, bias, Nk, Nq, C, p, unshared};
+    static int v2_env = -1;
+    if (v2_env < 0) {
+        const char* e = getenv("NPFK_SETCONV_V2");
+        v2_env = e ? atoi(e) : 1;
+    }
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (v2_env && C == 128 && Nk <= kV2MaxKeys && al16(v) && al16(wd) && al16(out) && al16(stats) && (!bias || al16(bias)) &&
+        ceil_div64(Nq, kV2Threads) <= 65535) {
+        // one task's value rows resident in shared memory, warp per 32 queries (see the kernel's header)
+        const size_t smem = ((size_t)Nk * 128 + kV2MaxKeys + 16 * kV2Slots * 32 + 16 * 64) * sizeof(float);
+        static bool attr_done = false;
+        if (!attr_done) {
+            cudaError_t e = cudaFuncSetAttribute(setconv_interp_fwd_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)((kV2MaxKeys * 128 + kV2MaxKeys + 16 * kV2Slots * 32 + 16 * 64) * sizeof(float)));
+            if (e != cudaSuccess) {
+                set_error("setconv_interp_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+                return NPFK_ERR_CUDA;
+            }
+            attr_done = true;
+        }
+        dim3 grid2((unsigned)ceil_div64(Nq, kV2Threads), B);
+        NPFK_LAUNCH(setconv_interp_fwd_v2_kernel, grid2, kV2Threads, smem, as_stream(stream), a, out, stats);
+        return check_launch("setconv_interp_fwd_v2");
+    }
     dim3 grid((unsigned)ceil_div64(Nq, kIQ), B);
     NPFK_LAUNCH(setconv_interp_fwd_kernel, grid, kIThreads, 0, as_stream(stream), a, out, stats);
     return check_launch("setconv_interp_fwd");

@@ -265,6 +265,10 @@ def test_setconv(B, Nk, Nq, C, unshared, shared_grid):
     (2, 48, 70, 32, 24, False, "grid"),       # induced grid -> targets
     (1, 192, 4096, 128, 128, False, "grid"),  # C3 shape of one task: most key chunks are skipped
     (2, 192, 130, 128, 128, False, "grid"),
+    (2, 100, 300, 128, 128, False, "random"),  # resident-value kernel, unsorted keys: window = every key, in rounds
+    (2, 64, 257, 128, 128, True, "grid"),      # resident-value kernel, UnsharedExpRBF
+    (3, 192, 1111, 128, 128, False, "grid_sorted_q"),   # sorted targets: one round per warp (the ConvCNP case)
+    (1, 256, 600, 128, 128, False, "clustered"),
     (2, 70, 200, 16, 160, False, "random"),   # unsorted keys, two channel passes of the output
     (2, 40, 90, 16, 24, True, "grid"),        # fork's UnsharedExpRBF
     (1, 1, 3, 2, 8, False, "random"),
@@ -283,6 +287,9 @@ def test_setconv_interp_hoisted_resizer(B, Nk, Nq, C, O_, unshared, keys):
     else:
         xk = torch.rand(B, Nk, 1, generator=g) * 2 - 1
     xq = torch.rand(B, Nq, 1, generator=g) * 2 - 1
+    if keys == "grid_sorted_q":
+        xk = torch.linspace(-1.5, 1.5, Nk).view(1, Nk, 1).expand(B, Nk, 1)
+        xq = torch.linspace(-1, 1, Nq).view(1, Nq, 1).expand(B, Nq, 1).contiguous()
     v = torch.randn(B, Nk, C, generator=g)
     sig = 3.0 / max(Nk, 8)
     theta = torch.full((2 if unshared else 1,), math.log(math.expm1(sig)))
