@@ -651,6 +651,220 @@ setconv_interp_fwd_v2_kernel(const InterpArgs a, float* __restrict__ out, float*
     }
 }
 
+
+// ------------------------------------------------------------------------------------------ backward, resident values
+// Same organisation as setconv_interp_fwd_v2_kernel: one task's value rows in shared memory, a warp per 32 queries.
+//   (a) lane = query: window and stabiliser as in the forward; dout_q . V_k for the keys of the warp's window, 32
+//       channels at a time (dout row quads from global memory, value rows as shared-memory broadcasts); d density_q =
+//       dout_q . wd; normalised weights into the [slot][query] table; the four length-scale sums of the tiled kernel;
+//   (b) lane = 4 channels: dV[slot] += w[slot][q] * dout_q accumulated in registers over the warp's 32 queries, then one
+//       16-byte red.global.add per (key, lane) -- a few hundred KB of reductions per task instead of one atomic per
+//       (CTA, key, channel); d bias / d wd column sums in the same sweep over the dout rows.
+// Windows wider than kB2Slots keys are walked in rounds (the dout rows are then re-read from L1 / L2).
+constexpr int kB2Slots = 16;
+
+__global__ void __launch_bounds__(kV2Threads, 1)
+setconv_interp_bwd_v2_kernel(const InterpArgs a, const float* __restrict__ stats, const float* __restrict__ dout,
+                             float* __restrict__ dv, float* __restrict__ dwd, float* __restrict__ dbias,
+                             float* __restrict__ dtheta) {
+    extern __shared__ __align__(16) float smem_v2[];
+    float* sV = smem_v2;                                   // [Nk][128]
+    float* sKeys = sV + (size_t)a.Nk * 128;                // [kV2MaxKeys]
+    float* sWq = sKeys + kV2MaxKeys;                       // [16 warps][kB2Slots][32]
+    float* sQ = sWq + 16 * kB2Slots * 32;                  // [16 warps][32]: density per query
+    float* sRed = sQ + 16 * 32;                            // [16 warps][2 * 128 + 2]
+    const int b = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int Nk = (int)a.Nk;
+    const float* xkb = a.xk + (int64_t)b * a.sxk;
+    {
+        const float4* src = reinterpret_cast<const float4*>(a.v + (int64_t)b * a.Nk * 128);
+        float4* dst = reinterpret_cast<float4*>(sV);
+        for (int i = threadIdx.x; i < Nk * 32; i += kV2Threads) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < Nk; i += kV2Threads) sKeys[i] = __ldg(xkb + i);
+    }
+    __syncthreads();
+    bool ok = true;
+    for (int i = threadIdx.x; i + 1 < Nk; i += kV2Threads) ok = ok && (sKeys[i] <= sKeys[i + 1]);
+    const bool sorted = __syncthreads_and(ok) != 0;
+
+    const float th0 = __ldg(a.theta);
+    const float sigma = 1e-5f + softplus_f(th0);
+    const float th1 = a.unshared ? __ldg(a.theta + 1) : th0;
+    const float sigma_d = a.unshared ? 1e-5f + softplus_f(th1) : sigma;
+    const int64_t q0 = (int64_t)blockIdx.x * kV2Threads + warp * 32;
+    const int nq = (int)max((int64_t)0, min((int64_t)32, a.Nq - q0));
+    const bool qv = lane < nq;
+    float4 db4 = make_float4(0.f, 0.f, 0.f, 0.f), dw4 = db4;      // column sums of this warp (lane = 4 channels)
+    float dsig0 = 0.f, dsig1 = 0.f;
+    if (nq > 0) {
+        const float xq = qv ? __ldg(a.xq + (int64_t)b * a.sxq + q0 + lane) : sKeys[0];
+        float* wq = sWq + warp * kB2Slots * 32;
+        float* sq = sQ + warp * 32;
+        const float* drow = dout + ((int64_t)b * a.Nq + q0 + (qv ? lane : 0)) * 128;      // this lane's query row
+
+        // ---- window and stabiliser (identical to the forward)
+        float m = 0.f;
+        int kl = 0, kr = Nk - 1;
+        if (sorted) {
+            int lo = 0, hi = Nk;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (sKeys[mid] < xq) lo = mid + 1; else hi = mid;
+            }
+            int near = lo < Nk ? lo : Nk - 1;
+            if (lo > 0 && (lo >= Nk || fabsf(sKeys[lo - 1] - xq) <= fabsf(sKeys[lo] - xq))) near = lo - 1;
+            const float dmin = fabsf(sKeys[near] - xq);
+            if (!a.unshared) m = interp_inp_d(dmin, sigma, a.p);
+            kl = kr = near;
+            if (a.unshared) {
+                while (kl > 0 && fmaxf(interp_inp_d(fabsf(sKeys[kl - 1] - xq), sigma, a.p),
+                                       interp_inp_d(fabsf(sKeys[kl - 1] - xq), sigma_d, a.p)) > kCutUnshared) --kl;
+                while (kr < Nk - 1 && fmaxf(interp_inp_d(fabsf(sKeys[kr + 1] - xq), sigma, a.p),
+                                            interp_inp_d(fabsf(sKeys[kr + 1] - xq), sigma_d, a.p)) > kCutUnshared) ++kr;
+            } else {
+                while (kl > 0 && interp_inp_d(fabsf(sKeys[kl - 1] - xq), sigma, a.p) - m > kCutShared) --kl;
+                while (kr < Nk - 1 && interp_inp_d(fabsf(sKeys[kr + 1] - xq), sigma, a.p) - m > kCutShared) ++kr;
+            }
+        } else if (!a.unshared) {
+            float dmin = CUDART_INF_F;
+            for (int k = 0; k < Nk; ++k) dmin = fminf(dmin, fabsf(sKeys[k] - xq));
+            m = interp_inp_d(dmin, sigma, a.p);
+        }
+        int wl = kl, wr = kr;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            wl = min(wl, __shfl_xor_sync(0xffffffffu, wl, o));
+            wr = max(wr, __shfl_xor_sync(0xffffffffu, wr, o));
+        }
+        const float dens = qv ? __ldg(stats + ((int64_t)b * a.Nq + q0 + lane) * 2) : 0.f;
+        const float lsum = qv ? __ldg(stats + ((int64_t)b * a.Nq + q0 + lane) * 2 + 1) : 1.f;
+        const float inv_l = a.unshared ? 1.f / (lsum + 1e-8f) : 1.f / lsum;
+        const float emax = a.unshared ? 1.f : expf(m);
+        sq[lane] = dens;
+
+        float ddens = 0.f, sA = 0.f, sB = 0.f, sDot = 0.f, sD = 0.f;
+        const float4* v4 = reinterpret_cast<const float4*>(sV);
+        for (int k0 = wl; k0 <= wr; k0 += kB2Slots) {
+            const int ns = min(kB2Slots, wr - k0 + 1);
+            const bool first = k0 == wl;
+            // ---- (a) lane = query: dp[s] = dout_q . V[k0 + s]
+            float dp[kB2Slots];
+#pragma unroll
+            for (int i = 0; i < kB2Slots; ++i) dp[i] = 0.f;
+#pragma unroll 1
+            for (int cb = 0; cb < 4; ++cb) {
+                float4 d[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) d[j] = qv ? __ldg(reinterpret_cast<const float4*>(drow) + cb * 8 + j)
+                                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+                if (first) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 w4 = __ldg(reinterpret_cast<const float4*>(a.wd) + cb * 8 + j);
+                        ddens = fmaf(d[j].x, w4.x, ddens); ddens = fmaf(d[j].y, w4.y, ddens);
+                        ddens = fmaf(d[j].z, w4.z, ddens); ddens = fmaf(d[j].w, w4.w, ddens);
+                    }
+                }
+#pragma unroll
+                for (int sidx = 0; sidx < kB2Slots; ++sidx) {
+                    if (sidx < ns) {
+                        const float4* vr = v4 + (size_t)(k0 + sidx) * 32 + cb * 8;
+                        float acc = dp[sidx];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 vv = vr[j];
+                            acc = fmaf(d[j].x, vv.x, acc); acc = fmaf(d[j].y, vv.y, acc);
+                            acc = fmaf(d[j].z, vv.z, acc); acc = fmaf(d[j].w, vv.w, acc);
+                        }
+                        dp[sidx] = acc;
+                    }
+                }
+            }
+            // weights of the slice, the table for (b), and the length-scale sums
+            __syncwarp();
+#pragma unroll
+            for (int sidx = 0; sidx < kB2Slots; ++sidx) {
+                float w = 0.f;
+                if (sidx < ns && qv) {
+                    const float d = fabsf(sKeys[k0 + sidx] - xq);
+                    const float inp = interp_inp_d(d, sigma, a.p);
+                    if (a.unshared) {
+                        const float i1 = interp_inp_d(d, sigma_d, a.p);
+                        w = expf(inp) * inv_l;
+                        sA = fmaf(w * dp[sidx], inp, sA);
+                        sD = fmaf(expf(i1), i1, sD);
+                    } else {
+                        const float e = expf(inp - m);
+                        w = e * inv_l;
+                        sA = fmaf(w * dp[sidx], inp - m, sA);
+                        sB = fmaf(w, inp - m, sB);
+                        sD = fmaf(e * emax, inp, sD);
+                    }
+                    sDot = fmaf(w, dp[sidx], sDot);
+                }
+                wq[sidx * 32 + lane] = w;
+            }
+            __syncwarp();
+            // ---- (b) lane = channels 4 lane .. 4 lane + 3
+            float4 dvacc[kB2Slots];
+#pragma unroll
+            for (int i = 0; i < kB2Slots; ++i) dvacc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4* dq4 = reinterpret_cast<const float4*>(dout + ((int64_t)b * a.Nq + q0) * 128) + lane;
+#pragma unroll 2
+            for (int q = 0; q < nq; ++q) {
+                const float4 d4 = __ldg(dq4 + (size_t)q * 32);
+                if (first) {
+                    const float dn = sq[q];
+                    db4.x += d4.x; db4.y += d4.y; db4.z += d4.z; db4.w += d4.w;
+                    dw4.x = fmaf(dn, d4.x, dw4.x); dw4.y = fmaf(dn, d4.y, dw4.y);
+                    dw4.z = fmaf(dn, d4.z, dw4.z); dw4.w = fmaf(dn, d4.w, dw4.w);
+                }
+#pragma unroll
+                for (int sidx = 0; sidx < kB2Slots; ++sidx) {
+                    if (sidx < ns) {
+                        const float w = wq[sidx * 32 + q];
+                        dvacc[sidx].x = fmaf(w, d4.x, dvacc[sidx].x); dvacc[sidx].y = fmaf(w, d4.y, dvacc[sidx].y);
+                        dvacc[sidx].z = fmaf(w, d4.z, dvacc[sidx].z); dvacc[sidx].w = fmaf(w, d4.w, dvacc[sidx].w);
+                    }
+                }
+            }
+            float* dvb = dv + ((int64_t)b * a.Nk + k0) * 128 + 4 * lane;
+#pragma unroll
+            for (int sidx = 0; sidx < kB2Slots; ++sidx)
+                if (sidx < ns)
+                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dvb + (size_t)sidx * 128),
+                                 "f"(dvacc[sidx].x), "f"(dvacc[sidx].y), "f"(dvacc[sidx].z), "f"(dvacc[sidx].w)
+                                 : "memory");
+        }
+        if (qv) {
+            if (a.unshared) {
+                dsig0 = sA * (-a.p / sigma);
+                dsig1 = (ddens - sDot * inv_l) * sD * (-a.p / sigma_d);
+            } else {
+                dsig0 = (sA - sDot * sB + ddens * sD) * (-a.p / sigma);
+            }
+        }
+        dsig0 = warp_sum(dsig0);
+        dsig1 = warp_sum(dsig1);
+    }
+    // ---- block reduction of d bias, d wd (lane = 4 channels) and d sigma, one atomic per (CTA, element)
+    float* r = sRed + warp * 260;
+    *reinterpret_cast<float4*>(r + 4 * lane) = db4;
+    *reinterpret_cast<float4*>(r + 128 + 4 * lane) = dw4;
+    if (lane == 0) { r[256] = dsig0; r[257] = dsig1; }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 258; i += kV2Threads) {
+        float sacc = 0.f;
+#pragma unroll
+        for (int w = 0; w < 16; ++w) sacc += sRed[w * 260 + i];
+        if (i < 128) { if (dbias) atomicAdd(dbias + i, sacc); }
+        else if (i < 256) atomicAdd(dwd + (i - 128), sacc);
+        else if (i == 256) atomicAdd(dtheta, sacc * sigmoid_f(th0));
+        else if (a.unshared) atomicAdd(dtheta + 1, sacc * sigmoid_f(th1));
+    }
+}
+
 }  // namespace npfk
 
 using namespace npfk;
@@ -712,6 +926,31 @@ int npfk_setconv_interp_bwd(const float* xk, int64_t sxk, const float* xq, int64
         attr_set = true;
     }
     InterpArgs a{xk, sxk, xq, sxq, v, theta, wd, nullptr, Nk, Nq, C, p, unshared};
+    static int v2_env = -1;
+    if (v2_env < 0) {
+        const char* e = getenv("NPFK_SETCONV_V2");
+        v2_env = e ? atoi(e) : 1;
+    }
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (v2_env && C == 128 && Nk <= kV2MaxKeys && al16(v) && al16(wd) && al16(dout) && al16(dv) && al16(stats) &&
+        ceil_div64(Nq, kV2Threads) <= 65535) {
+        const size_t fl = (size_t)kV2MaxKeys + 16 * kB2Slots * 32 + 16 * 32 + 16 * 260;
+        const size_t smem = ((size_t)Nk * 128 + fl) * sizeof(float);
+        static bool attr2 = false;
+        if (!attr2) {
+            cudaError_t e = cudaFuncSetAttribute(setconv_interp_bwd_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)(((size_t)kV2MaxKeys * 128 + fl) * sizeof(float)));
+            if (e != cudaSuccess) {
+                set_error("setconv_interp_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+                return NPFK_ERR_CUDA;
+            }
+            attr2 = true;
+        }
+        dim3 grid2((unsigned)ceil_div64(Nq, kV2Threads), B);
+        NPFK_LAUNCH(setconv_interp_bwd_v2_kernel, grid2, kV2Threads, smem, as_stream(stream), a, stats, dout, dv, dwd, dbias,
+                    dtheta);
+        return check_launch("setconv_interp_bwd_v2");
+    }
     dim3 grid((unsigned)ceil_div64(Nq, kIQ), B);
     NPFK_LAUNCH(setconv_interp_bwd_kernel, grid, kIThreads, sizeof(InterpBwdSmem), as_stream(stream), a, stats, dout, dv,
                 dwd, dbias, dtheta);
