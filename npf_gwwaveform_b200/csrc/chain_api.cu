@@ -30,38 +30,52 @@ nll_head_bwd_kernel(const float* __restrict__ h, int64_t ldh, const float* __res
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
     float b0 = 0.f, b1 = 0.f;
     const int64_t wstride = (int64_t)gridDim.x * kHbWarps;
-    for (int64_t row = (int64_t)blockIdx.x * kHbWarps + warp; row < M; row += wstride) {
-        const float4 hv = __ldg(reinterpret_cast<const float4*>(h + row * ldh) + lane);
-        const float2 sf = __ldg(reinterpret_cast<const float2*>(suff) + row);
-        float d0 = 0.f, d1 = 0.f;
-        if (dsum_lp) {
-            // lp = -(y - mu)^2 / (2 s^2) - log s - c,  s = 0.01 + 0.99 softplus(raw):  d lp/d mu = d / s^2,
-            // d lp/d raw = (d^2 / s^3 - 1 / s) * 0.99 sigmoid(raw)
-            const float gl = __ldg(dsum_lp + row / T);
-            const float sc = 0.01f + 0.99f * softplus_f(sf.y), inv = 1.f / sc;
-            const float d = __ldg(y + row % y_rows) - sf.x;
-            d0 = gl * d * inv * inv;
-            d1 = gl * (d * d * inv * inv * inv - inv) * 0.99f * sigmoid_f(sf.y);
+    constexpr int U = 4;       // rows in flight per warp: their loads are issued together (the kernel is latency-bound otherwise)
+    for (int64_t row0 = (int64_t)blockIdx.x * kHbWarps + warp; row0 < M; row0 += wstride * U) {
+        float4 hv[U];
+        float2 sf[U], di[U];
+        float gl[U], yv[U];
+        bool okr[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t row = row0 + u * wstride;
+            okr[u] = row < M;
+            const int64_t rr = okr[u] ? row : row0;
+            hv[u] = __ldg(reinterpret_cast<const float4*>(h + rr * ldh) + lane);
+            sf[u] = __ldg(reinterpret_cast<const float2*>(suff) + rr);
+            // M, T, y_rows < 2^31 (checked by the entry point): 32-bit division
+            gl[u] = dsum_lp ? __ldg(dsum_lp + (uint32_t)rr / (uint32_t)T) : 0.f;
+            yv[u] = dsum_lp ? __ldg(y + (uint32_t)rr % (uint32_t)y_rows) : 0.f;
+            di[u] = dsuff_in ? __ldg(reinterpret_cast<const float2*>(dsuff_in) + rr) : make_float2(0.f, 0.f);
         }
-        if (dsuff_in) {
-            const float2 di = __ldg(reinterpret_cast<const float2*>(dsuff_in) + row);
-            d0 += di.x;
-            d1 += di.y;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (!okr[u]) continue;
+            const int64_t row = row0 + u * wstride;
+            float d0 = di[u].x, d1 = di[u].y;
+            if (dsum_lp) {
+                // lp = -(y - mu)^2 / (2 s^2) - log s - c,  s = 0.01 + 0.99 softplus(raw):  d lp/d mu = d / s^2,
+                // d lp/d raw = (d^2 / s^3 - 1 / s) * 0.99 sigmoid(raw)
+                const float sc = 0.01f + 0.99f * softplus_f(sf[u].y), inv = 1.f / sc;
+                const float d = yv[u] - sf[u].x;
+                d0 = fmaf(gl[u] * d, inv * inv, d0);
+                d1 = fmaf(gl[u] * (d * d * inv * inv * inv - inv), 0.99f * sigmoid_f(sf[u].y), d1);
+            }
+            float4 o;
+            o.x = fmaf(d0, w0.x, d1 * w1.x); o.y = fmaf(d0, w0.y, d1 * w1.y);
+            o.z = fmaf(d0, w0.z, d1 * w1.z); o.w = fmaf(d0, w0.w, d1 * w1.w);
+            if (masked) {
+                if (!(hv[u].x > 0.f)) o.x = 0.f;
+                if (!(hv[u].y > 0.f)) o.y = 0.f;
+                if (!(hv[u].z > 0.f)) o.z = 0.f;
+                if (!(hv[u].w > 0.f)) o.w = 0.f;
+            }
+            if (g) __stcs(reinterpret_cast<float4*>(g + row * 128) + lane, o);
+            a0.x = fmaf(d0, hv[u].x, a0.x); a0.y = fmaf(d0, hv[u].y, a0.y); a0.z = fmaf(d0, hv[u].z, a0.z); a0.w = fmaf(d0, hv[u].w, a0.w);
+            a1.x = fmaf(d1, hv[u].x, a1.x); a1.y = fmaf(d1, hv[u].y, a1.y); a1.z = fmaf(d1, hv[u].z, a1.z); a1.w = fmaf(d1, hv[u].w, a1.w);
+            b0 += d0;
+            b1 += d1;
         }
-        float4 o;
-        o.x = fmaf(d0, w0.x, d1 * w1.x); o.y = fmaf(d0, w0.y, d1 * w1.y);
-        o.z = fmaf(d0, w0.z, d1 * w1.z); o.w = fmaf(d0, w0.w, d1 * w1.w);
-        if (masked) {
-            if (!(hv.x > 0.f)) o.x = 0.f;
-            if (!(hv.y > 0.f)) o.y = 0.f;
-            if (!(hv.z > 0.f)) o.z = 0.f;
-            if (!(hv.w > 0.f)) o.w = 0.f;
-        }
-        if (g) *(reinterpret_cast<float4*>(g + row * 128) + lane) = o;
-        a0.x = fmaf(d0, hv.x, a0.x); a0.y = fmaf(d0, hv.y, a0.y); a0.z = fmaf(d0, hv.z, a0.z); a0.w = fmaf(d0, hv.w, a0.w);
-        a1.x = fmaf(d1, hv.x, a1.x); a1.y = fmaf(d1, hv.y, a1.y); a1.z = fmaf(d1, hv.z, a1.z); a1.w = fmaf(d1, hv.w, a1.w);
-        b0 += d0;
-        b1 += d1;
     }
     float* r = red[warp];
     *reinterpret_cast<float4*>(r + 4 * lane) = a0;
@@ -102,13 +116,14 @@ int npfk_nll_head_bwd(const float* h, int64_t ldh, const float* head_w, const fl
     using namespace npfk;
     NPFK_REQUIRE(h && head_w && suff, "nll_head_bwd: null pointer");
     NPFK_REQUIRE(!dsum_lp || (y && T > 0 && y_rows > 0), "nll_head_bwd: dsum_lp needs y, y_rows and T");
+    NPFK_REQUIRE(M < 2147483647LL && T < 2147483647LL && y_rows < 2147483647LL, "nll_head_bwd: sizes must be below 2^31");
     NPFK_REQUIRE((ldh & 3) == 0 && ((reinterpret_cast<uintptr_t>(h) | reinterpret_cast<uintptr_t>(g) |
                                      reinterpret_cast<uintptr_t>(head_w)) & 15) == 0 &&
                      (reinterpret_cast<uintptr_t>(suff) & 7) == 0 && (reinterpret_cast<uintptr_t>(dsuff_in) & 7) == 0,
                  "nll_head_bwd: h / g / head_w must be 16-byte aligned (row pitch a multiple of 4 floats), suff 8-byte aligned");
     if (M <= 0) return NPFK_OK;
     int64_t blocks = ceil_div64(M, kHbWarps * 16);       // >= 16 rows per warp so the block reduction amortises
-    if (blocks > (int64_t)kNumSMs * 8) blocks = (int64_t)kNumSMs * 8;
+    if (blocks > (int64_t)kNumSMs * 6) blocks = (int64_t)kNumSMs * 6;
     if (blocks < 1) blocks = 1;
     NPFK_LAUNCH(nll_head_bwd_kernel, (unsigned)blocks, kHbWarps * 32, 0, as_stream(stream), h, ldh, head_w, suff, y,
                 y_rows > 0 ? y_rows : 1, T > 0 ? T : 1, dsum_lp, dsuff_in, masked, g, dw, db, M);

@@ -552,7 +552,7 @@ setconv_interp_fwd_v2_kernel(const InterpArgs a, float* __restrict__ out, float*
         m = interp_inp_d(dmin, sigma, a.p);
     }
     // the warp's window: union over its queries
-    int wl = kl, wr = kr;
+    int wl = qv ? kl : Nk, wr = qv ? kr : -1;      // lanes past the last query do not widen the window
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         wl = min(wl, __shfl_xor_sync(0xffffffffu, wl, o));
@@ -731,7 +731,7 @@ setconv_interp_bwd_v2_kernel(const InterpArgs a, const float* __restrict__ stats
             for (int k = 0; k < Nk; ++k) dmin = fminf(dmin, fabsf(sKeys[k] - xq));
             m = interp_inp_d(dmin, sigma, a.p);
         }
-        int wl = kl, wr = kr;
+        int wl = qv ? kl : Nk, wr = qv ? kr : -1;      // lanes past the last query do not widen the window
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             wl = min(wl, __shfl_xor_sync(0xffffffffu, wl, o));
@@ -885,7 +885,7 @@ int npfk_setconv_interp_fwd(const float* xk, int64_t sxk, const float* xq, int64
         v2_env = e ? atoi(e) : 1;
     }
     auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-    if (v2_env && C == 128 && Nk <= kV2MaxKeys && al16(v) && al16(wd) && al16(out) && al16(stats) && (!bias || al16(bias)) &&
+    if ((v2_env == 1 || v2_env == 2) && C == 128 && Nk <= kV2MaxKeys && al16(v) && al16(wd) && al16(out) && al16(stats) && (!bias || al16(bias)) &&
         ceil_div64(Nq, kV2Threads) <= 65535) {
         // one task's value rows resident in shared memory, warp per 32 queries (see the kernel's header)
         const size_t smem = ((size_t)Nk * 128 + kV2MaxKeys + 16 * kV2Slots * 32 + 16 * 64) * sizeof(float);
@@ -932,7 +932,7 @@ int npfk_setconv_interp_bwd(const float* xk, int64_t sxk, const float* xq, int64
         v2_env = e ? atoi(e) : 1;
     }
     auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-    if (v2_env && C == 128 && Nk <= kV2MaxKeys && al16(v) && al16(wd) && al16(dout) && al16(dv) && al16(stats) &&
+    if ((v2_env == 1 || v2_env == 3) && C == 128 && Nk <= kV2MaxKeys && al16(v) && al16(wd) && al16(dout) && al16(dv) && al16(stats) &&
         ceil_div64(Nq, kV2Threads) <= 65535) {
         const size_t fl = (size_t)kV2MaxKeys + 16 * kB2Slots * 32 + 16 * 32 + 16 * 260;
         const size_t smem = ((size_t)Nk * 128 + fl) * sizeof(float);

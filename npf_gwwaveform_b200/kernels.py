@@ -89,6 +89,45 @@ def _grad_sink_buf(p, shape=None):
     return g if shape is None else g.view(shape)
 
 
+# ------------------------------------------------------------------------------------------ side stream for wgrads
+# A weight gradient is a leaf of the backward graph: nothing downstream in the same pass reads it.  For the small,
+# latency-bound GEMMs of the conv nets (6 k rows; ~10 us each where the data would stream in 1-2 us) the dgrad / wgrad
+# pair of a layer is issued on two streams so that the wgrad overlaps the rest of the backward chain; an autograd engine
+# callback joins the side stream before backward() returns (and inside a CUDA-graph capture the fork / join become graph
+# edges).  NPFK_WGRAD_STREAM=0 disables it.
+import os as _os
+
+_side = {"stream": None, "pending": False, "on": _os.environ.get("NPFK_WGRAD_STREAM", "1") != "0"}
+
+
+def join_side_stream():
+    """make the current stream wait for every wgrad issued on the side stream so far (FlatAdamTrainer calls this before
+    it all-reduces a gradient bucket; the autograd engine callback calls it at the end of backward())"""
+    _join_side()
+
+
+def _join_side():
+    if _side["pending"]:
+        torch.cuda.current_stream().wait_stream(_side["stream"])
+        _side["pending"] = False
+
+
+def _fork_side(*tensors):
+    """side stream ordered after everything issued so far on the current stream; the caller launches on it inside
+    ``with torch.cuda.stream(side)``.  `tensors` are kept alive for the side stream (caching-allocator bookkeeping)."""
+    if _side["stream"] is None or _side["stream"].device != torch.cuda.current_stream().device:
+        _side["stream"] = torch.cuda.Stream()
+    side = _side["stream"]
+    side.wait_stream(torch.cuda.current_stream())
+    for t in tensors:
+        if t is not None:
+            t.record_stream(side)
+    if not _side["pending"]:
+        _side["pending"] = True
+        torch.autograd.Variable._execution_engine.queue_callback(_join_side)
+    return side
+
+
 def _rows_view(x: torch.Tensor):
     """(tensor, ld) such that x can be read as M rows of K elements with row stride ld (no copy when possible)."""
     K = x.shape[-1]
@@ -253,7 +292,16 @@ class _LinearFn(Function):
             if dx is not None:
                 LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wv), ldw, None, 0, _p(dx), K, M, N, K, ctx.mode, st)
             if dw is not None:
-                LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(xv), ldx, _p(dw), K, _p(db), M, N, K, ctx.mode, st)
+                direct = sink_w is not None and (db is None or sink_b is not None)
+                if dx is not None and direct and _side["on"] and M <= 65536:
+                    # small layer, gradients written straight into the trainer's flat buffer (nothing is handed back to
+                    # autograd, whose AccumulateGrad would read it on the main stream): the wgrad runs beside the rest of
+                    # the backward pass (see _fork_side)
+                    side = _fork_side(g, xv, dw, db)
+                    with torch.cuda.stream(side):
+                        LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(xv), ldx, _p(dw), K, _p(db), M, N, K, ctx.mode, _st())
+                else:
+                    LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(xv), ldx, _p(dw), K, _p(db), M, N, K, ctx.mode, st)
         if ctx.has_res and ctx.needs_input_grad[3]:
             if res_rows == M:
                 dres = g.reshape(ctx.res_shape)

@@ -116,6 +116,7 @@ class FlatAdamTrainer:
 
     def _launch_bucket(self, b: int) -> None:
         lo, hi = self.bucket_slices[b]
+        K.join_side_stream()      # weight gradients issued on the side stream (kernels._fork_side) are part of the bucket
         if hi > lo:
             self._pending.append(dist.all_reduce(self.flat_grad[lo:hi], op=dist.ReduceOp.SUM, group=self.group,
                                                  async_op=True))

@@ -90,7 +90,8 @@ ORACLE_KW = {"ConvCNP_unet": dict(unet=True, density_induced=64), "ConvCNP": dic
 
 
 @pytest.mark.parametrize("name,B,Nc,Nt", [
-    ("CNP", 4, 64, 128), ("AttnCNP", 3, 77, 301), ("ConvCNP", 2, 50, 200), ("ConvCNP_unet", 3, 33, 129),
+    ("CNP", 4, 64, 128), ("AttnCNP", 3, 77, 301), ("ConvCNP", 3, 50, 200), ("ConvCNP", 2, 50, 210),
+    ("ConvCNP", 3, 60, 333), ("ConvCNP_unet", 3, 33, 129),
     ("LNP", 2, 10, 40), ("AttnLNP", 2, 40, 150), ("AttnCNP", 2, 0, 33), ("CNP", 2, 0, 9), ("ConvCNP", 2, 0, 20),
     ("AttnCNP", 1, 1, 1), ("ConvLNP", 2, 40, 150), ("ConvLNP_both", 3, 30, 77),
 ])
@@ -142,6 +143,11 @@ def test_against_oracle_notebook_width(name, B, Nc, Nt):
         if k in ref_grads:
             g = ref_grads[k]
             err = float((p.grad.cpu().double() - g).abs().max()) / max(float(g.abs().max()), 1e-3 * gmax)
+            # (ConvCNP ran with (B, Nc, Nt) = (2, 50, 200) until the resident-value SetConv kernels changed the summation
+            # order of the interpolation: outputs moved by 1e-7 (both orders are 1.5e-7 from float64,
+            # tools/setconv_v2_check.py), one pre-activation crossed a ReLU kink and the smallest gradient of the model,
+            # cntxt_to_induced's length scale, moved by 8e-6 of the largest gradient = 8e-3 of this test's floored
+            # denominator; the three neighbouring shapes now in the list are clear of such coincidences.)
             # (ConvCNP_unet runs with B=3: at B=2 one pre-activation of block 3's norm2 lands within fp32 rounding of
             # the ReLU kink, the float64 oracle and the fp32 kernels take different sides and every gradient upstream
             # of it moves by ~1e-3; tools/unet_grad_debug.py shows <=1.5e-6 everywhere at B=3 and B=4.)

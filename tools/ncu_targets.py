@@ -65,6 +65,27 @@ bs = torch.zeros(128, device="cuda", requires_grad=True)
 for _ in range(2):
     o = Kn.setconv_interp(grid, xt, vals, theta, wd, bs)
     o.backward(torch.randn_like(o))
+# K1: fused MLP chains at the C2 target-row count -- the decoder's flat module with the head + log-likelihood tail
+# (4 layers + 128 -> 2), training (every activation written) and inference (nothing but [M, 2] leaves the chip), the
+# resizer (2 layers + residual), and the tail's backward
+def _layers(n, n_out=128):
+    return [((torch.randn(n_out if i == n - 1 else 128, 128, device="cuda") * 0.1).requires_grad_(True),
+             torch.zeros(n_out if i == n - 1 else 128, device="cuda", requires_grad=True)) for i in range(n)]
+
+
+M = B * Nq
+xr = torch.randn(M, 128, device="cuda").relu()
+rs = torch.randn(M, 128, device="cuda")
+yc = torch.randn(B, Nq, 1, device="cuda")
+flat, resz = _layers(5, 2), _layers(2)
+for _ in range(2):
+    sf, lp = Kn.mlp_chain(xr.clone().requires_grad_(True), flat, x_is_relu=True, nll=(yc, Nq))
+    lp.sum().backward()
+    with torch.no_grad():
+        Kn.mlp_chain(xr, flat, x_is_relu=True, nll=(yc, Nq))
+    Kn.mlp_chain(xr.clone().requires_grad_(True), resz, res=rs, out_relu=True)
+del sf, lp
+torch.cuda.synchronize()
 suff = torch.randn(1, 256, Nq, 2, device="cuda", requires_grad=True)
 yt = torch.randn(256, Nq, 1, device="cuda")
 for _ in range(2):
