@@ -218,7 +218,7 @@ KERNEL_FAMILIES = {
     "linear wgrad": (["npfk_linear_bwd_dw"], "hbm", "tc_gemm_tn_kernel"),
     "residual + LayerNorm": (["npfk_add_layernorm_fwd", "npfk_add_layernorm_bwd"], "hbm", "add_layernorm_fwd"),
     "Gaussian log-likelihood": (["npfk_gauss_nll_fwd", "npfk_gauss_nll_bwd"], "hbm", "gauss_nll_fwd_kernel"),
-    "SetConv grid->target": (["npfk_setconv_interp_fwd", "npfk_setconv_interp_bwd"], "hbm", "setconv_interp_fwd_kernel"),
+    "SetConv grid->target": (["npfk_setconv_interp_fwd", "npfk_setconv_interp_bwd"], "hbm", "setconv_interp_fwd_v2_kernel"),
 }
 
 

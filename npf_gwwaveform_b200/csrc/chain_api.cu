@@ -48,19 +48,29 @@ nll_head_bwd_kernel(const float* __restrict__ h, int64_t ldh, const float* __res
             yv[u] = dsum_lp ? __ldg(y + (uint32_t)rr % (uint32_t)y_rows) : 0.f;
             di[u] = dsuff_in ? __ldg(reinterpret_cast<const float2*>(dsuff_in) + rr) : make_float2(0.f, 0.f);
         }
+        // the per-row scalars (softplus / sigmoid / reciprocal) are evaluated by ONE lane per row (lane u for row u) and
+        // broadcast: all 32 lanes doing the same transcendental work made the kernel XU-bound (ncu: xu 29 %, 60 % of HBM)
+        float my0 = 0.f, my1 = 0.f;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
+            if (lane == u) {
+                my0 = di[u].x;
+                my1 = di[u].y;
+                if (dsum_lp) {
+                    // lp = -(y - mu)^2 / (2 s^2) - log s - c,  s = 0.01 + 0.99 softplus(raw):  d lp/d mu = d / s^2,
+                    // d lp/d raw = (d^2 / s^3 - 1 / s) * 0.99 sigmoid(raw)
+                    const float sc = 0.01f + 0.99f * softplus_f(sf[u].y), inv = 1.f / sc;
+                    const float d = yv[u] - sf[u].x;
+                    my0 = fmaf(gl[u] * d, inv * inv, my0);
+                    my1 = fmaf(gl[u] * (d * d * inv * inv * inv - inv), 0.99f * sigmoid_f(sf[u].y), my1);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const float d0 = __shfl_sync(0xffffffffu, my0, u), d1 = __shfl_sync(0xffffffffu, my1, u);
             if (!okr[u]) continue;
             const int64_t row = row0 + u * wstride;
-            float d0 = di[u].x, d1 = di[u].y;
-            if (dsum_lp) {
-                // lp = -(y - mu)^2 / (2 s^2) - log s - c,  s = 0.01 + 0.99 softplus(raw):  d lp/d mu = d / s^2,
-                // d lp/d raw = (d^2 / s^3 - 1 / s) * 0.99 sigmoid(raw)
-                const float sc = 0.01f + 0.99f * softplus_f(sf[u].y), inv = 1.f / sc;
-                const float d = yv[u] - sf[u].x;
-                d0 = fmaf(gl[u] * d, inv * inv, d0);
-                d1 = fmaf(gl[u] * (d * d * inv * inv * inv - inv), 0.99f * sigmoid_f(sf[u].y), d1);
-            }
             float4 o;
             o.x = fmaf(d0, w0.x, d1 * w1.x); o.y = fmaf(d0, w0.y, d1 * w1.y);
             o.z = fmaf(d0, w0.z, d1 * w1.z); o.w = fmaf(d0, w0.w, d1 * w1.w);
