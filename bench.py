@@ -462,7 +462,7 @@ def measure_training(args, workload, dev, rank, world, scaling, steps, warmup, w
     torch.manual_seed(0)                            # identical initial weights on every rank
     model = build_product(model_name, 128, nz=nz).to(dev).train()
     crit = (npf.ELBOLossLNPF if "LNP" in model_name else npf.CNPFLoss)().train()
-    trainer = FlatAdamTrainer(model, crit, lr=1e-3)
+    trainer = FlatAdamTrainer(model, crit, lr=1e-3, n_buckets=int(os.environ.get("NPFK_BUCKETS", "2")))
 
     # synthetic shard resident in HBM for `value`, pinned on the host for `e2e`.  weak: every rank draws its own tasks
     # (seed 1234 + rank); strong: rank r takes its slice of ONE global batch (seed 1234), micro-batch by micro-batch
