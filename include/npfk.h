@@ -208,7 +208,7 @@ int npfk_gather_rows(const float* src, const int64_t* idx, float* dst, int B, in
 /* per-channel batch statistics of x:[rows,C]: stats[0:C] = mean, stats[C:2C] = biased variance.
  * If running_mean != NULL: running <- (1-momentum) running + momentum * (mean, unbiased var).
  * If num_batches_tracked != NULL: *num_batches_tracked += 1 (BatchNorm1d's int64 buffer). */
-int npfk_bn_stats(const float* x, int64_t rows, int C, double* scratch /* [2C] */, float* stats,
+int npfk_bn_stats(const float* x, int64_t rows, int C, double* scratch /* [2C + 1], see npfk_workspace_bytes */, float* stats,
                   float* running_mean, float* running_var, float momentum, int64_t* num_batches_tracked,
                   void* stream);
 /* y[b,l,c] = sum_j w[c,j] * h[b,l+j-ks/2,c] + bias[c] + res[b,l,c]   (zero padding of h outside [0,L))

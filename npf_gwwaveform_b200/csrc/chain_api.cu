@@ -144,7 +144,7 @@ int npfk_nll_head_bwd(const float* h, int64_t ldh, const float* head_w, const fl
 int64_t npfk_workspace_bytes(int op, int64_t d0, int64_t d1, int64_t d2) {
     switch (op) {
         case NPFK_OP_MHA_BWD: return 4 * npfk_mha_bwd_ws_floats((int)d0, d1, (int)d2);   // (B, Nq, H)
-        case NPFK_OP_BN_STATS: return 16 * d0;                                           // (C): double scratch [2C]
+        case NPFK_OP_BN_STATS: return 16 * d0 + 8;                                       // (C): double sums [2C] + ticket
         default: return 0;
     }
 }

@@ -10,43 +10,77 @@
 namespace npfk {
 
 // ------------------------------------------------------------------------- batch statistics
-// grid (row chunks, channel tiles of 128); a thread loads its kBnRows values first (independent loads), then sums
-constexpr int kBnRows = 32;
-__global__ void __launch_bounds__(128)
-bn_partial_kernel(const float* __restrict__ x, int64_t rows, int C, double* __restrict__ scratch) {
-    const int c = blockIdx.y * 128 + threadIdx.x;
-    if (c >= C) return;
-    const int64_t r0 = (int64_t)blockIdx.x * kBnRows;
-    float v[kBnRows];
-#pragma unroll
-    for (int i = 0; i < kBnRows; ++i) v[i] = (r0 + i < rows) ? __ldg(x + (r0 + i) * C + c) : 0.f;
-    double s = 0.0, ss = 0.0;
-#pragma unroll
-    for (int i = 0; i < kBnRows; ++i) {
-        const double t = (double)v[i];
-        s += t;
-        ss += t * t;
+// One kernel for the batch statistics: grid (row chunks of kBnRows, channel tiles of 128), 8 warps per block; a lane
+// owns 4 consecutive channels (16-byte loads), a warp walks every 8th row of the chunk, the warps' partial sums are
+// reduced in shared memory and added to the double-precision scratch with ONE atomic per (block, channel).  The last
+// block to finish (ticket in scratch[2C]) turns the sums into mean / biased variance and updates the running
+// statistics, so no second launch is needed.  (Was: one thread per (32 rows, channel) with two double atomics each --
+// 192-way contention per address at the UNet shapes, 13 us -- plus a finalize launch of 4 us.)
+constexpr int kBnRows = 128;
+__global__ void __launch_bounds__(256)
+bn_stats_kernel(const float* __restrict__ x, int64_t rows, int C, double* __restrict__ scratch, float* __restrict__ stats,
+                float* __restrict__ running_mean, float* __restrict__ running_var, float momentum,
+                long long* __restrict__ num_batches_tracked) {
+    __shared__ double red[8][128][2];
+    __shared__ bool is_last;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c0 = blockIdx.y * 128 + 4 * lane;
+    const int64_t r0 = (int64_t)blockIdx.x * kBnRows, r1 = min(rows, r0 + kBnRows);
+    double s[4] = {0.0, 0.0, 0.0, 0.0}, ss[4] = {0.0, 0.0, 0.0, 0.0};      // double throughout, as the statistics feed 1e-4 parity gates
+    if (c0 + 3 < C && (C & 3) == 0) {
+        for (int64_t r = r0 + warp; r < r1; r += 8) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(x + r * C + c0));
+            const double d0 = v.x, d1 = v.y, d2 = v.z, d3 = v.w;
+            s[0] += d0; s[1] += d1; s[2] += d2; s[3] += d3;
+            ss[0] = fma(d0, d0, ss[0]); ss[1] = fma(d1, d1, ss[1]);
+            ss[2] = fma(d2, d2, ss[2]); ss[3] = fma(d3, d3, ss[3]);
+        }
+    } else {
+        for (int64_t r = r0 + warp; r < r1; r += 8)
+            for (int j = 0; j < 4; ++j)
+                if (c0 + j < C) {
+                    const double v = (double)__ldg(x + r * C + c0 + j);
+                    s[j] += v;
+                    ss[j] = fma(v, v, ss[j]);
+                }
     }
-    atomicAdd(scratch + c, s);
-    atomicAdd(scratch + C + c, ss);
-}
-
-__global__ void bn_finalize_kernel(const double* __restrict__ scratch, int64_t rows, int C, float* __restrict__ stats,
-                                   float* __restrict__ running_mean, float* __restrict__ running_var, float momentum,
-                                   long long* __restrict__ num_batches_tracked) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    if (c == 0 && num_batches_tracked) *num_batches_tracked += 1;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        red[warp][4 * lane + j][0] = s[j];
+        red[warp][4 * lane + j][1] = ss[j];
+    }
+    __syncthreads();
+    {
+        const int ch = threadIdx.x & 127, which = threadIdx.x >> 7;      // 256 threads = 128 channels x {sum, sum of squares}
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[w][ch][which];
+        const int c = blockIdx.y * 128 + ch;
+        if (c < C) atomicAdd(scratch + which * C + c, t);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned total = gridDim.x * gridDim.y;
+        const unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(scratch + 2 * C), 1u);
+        is_last = ticket == total - 1;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    if (threadIdx.x == 0 && num_batches_tracked) *num_batches_tracked += 1;
     const double n = (double)rows;
-    const double mean = scratch[c] / n;
-    double var = scratch[C + c] / n - mean * mean;
-    if (var < 0.0) var = 0.0;
-    stats[c] = (float)mean;
-    stats[C + c] = (float)var;
-    if (running_mean) {
-        const double unbiased = rows > 1 ? var * n / (n - 1.0) : var;
-        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
-        running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const double mean = __ldcg(scratch + c) / n;
+        double var = __ldcg(scratch + C + c) / n - mean * mean;
+        if (var < 0.0) var = 0.0;
+        stats[c] = (float)mean;
+        stats[C + c] = (float)var;
+        if (running_mean) {
+            const double unbiased = rows > 1 ? var * n / (n - 1.0) : var;
+            running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
+            running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+        }
     }
 }
 
@@ -425,19 +459,17 @@ int npfk_bn_stats(const float* x, int64_t rows, int C, double* scratch, float* s
     NPFK_REQUIRE(rows > 0 && C > 0, "bn_stats: bad shape");
     NPFK_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_stats: running stats must come in pairs");
     cudaStream_t st = as_stream(stream);
-    cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * C, st);
+    cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(double) * (2 * C + 1), st);      // sums + the blocks-done ticket
     if (e != cudaSuccess) {
         set_error("bn_stats: memset: %s", cudaGetErrorString(e));
         return NPFK_ERR_CUDA;
     }
     NPFK_REQUIRE(C <= 65535 * 128, "bn_stats: too many channels");
     dim3 pgrid((unsigned)ceil_div64(rows, kBnRows), (unsigned)((C + 127) / 128));
-    NPFK_LAUNCH(bn_partial_kernel, pgrid, 128, 0, st, x, rows, C, scratch);
-    int rc = check_launch("bn_partial");
-    if (rc != NPFK_OK) return rc;
-    NPFK_LAUNCH(bn_finalize_kernel, (C + 127) / 128, 128, 0, st, scratch, rows, C, stats, running_mean, running_var,
-                momentum, reinterpret_cast<long long*>(num_batches_tracked));
-    return check_launch("bn_finalize");
+    NPFK_REQUIRE(pgrid.x <= 2147483647u / pgrid.y, "bn_stats: grid too large");
+    NPFK_LAUNCH(bn_stats_kernel, pgrid, 256, 0, st, x, rows, C, scratch, stats, running_mean, running_var, momentum,
+                reinterpret_cast<long long*>(num_batches_tracked));
+    return check_launch("bn_stats");
 }
 
 int npfk_dwconv_fwd(const float* x, const float* mean, const float* var, const float* gamma, const float* beta,

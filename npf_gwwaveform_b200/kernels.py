@@ -876,7 +876,7 @@ class _NormActDwConvFn(Function):
 
                 # local statistics (no running-stat update), then one all-reduce of [sum x | sum x^2 | count]
                 stats = torch.empty(2 * C, device=x.device, dtype=torch.float32)
-                scratch = torch.empty(2 * C, device=x.device, dtype=torch.float64)
+                scratch = torch.empty(2 * C + 1, device=x.device, dtype=torch.float64)
                 LIB.call("npfk_bn_stats", _p(x), B * L, C, _p(scratch), _p(stats), None, None, 0.0, None, st)
                 n_loc = float(B * L)
                 m_l, v_l = stats[:C].double(), stats[C:].double()
@@ -897,7 +897,7 @@ class _NormActDwConvFn(Function):
                 ctx.sync = (sync[0], n_loc, n_tot.float())
             elif training:
                 stats = torch.empty(2 * C, device=x.device, dtype=torch.float32)
-                scratch = torch.empty(2 * C, device=x.device, dtype=torch.float64)
+                scratch = torch.empty(2 * C + 1, device=x.device, dtype=torch.float64)
                 LIB.call("npfk_bn_stats", _p(x), B * L, C, _p(scratch), _p(stats), _p(running_mean), _p(running_var),
                          float(momentum), _p(num_batches_tracked), st)
                 mean, var = stats[:C], stats[C:]
