@@ -129,6 +129,33 @@ def _fork_side(*tensors):
     return side
 
 
+# ------------------------------------------------------------------------------------------ zero arena
+# "+=" outputs of the backward kernels (weight / bias / length-scale gradients, BatchNorm sums, dV of the SetConvs) need
+# zero-filled buffers.  Under FlatAdamTrainer they are slices of ONE arena that the trainer zeroes once per step, instead
+# of one fill kernel per buffer (23 fills per ConvCNP-UNet step).  Outside a trainer step `zeros` is torch.zeros.
+_arena = {"buf": None, "off": 0}
+
+
+def set_zero_arena(buf: Optional[torch.Tensor]) -> None:
+    """``buf``: a float32 tensor that the caller has JUST zeroed on the current stream (or None to switch the arena off).
+    Every slice handed out lives until the caller zeroes the arena again."""
+    _arena["buf"], _arena["off"] = buf, 0
+
+
+def zeros(*shape, device=None) -> torch.Tensor:
+    n = 1
+    for d in shape:
+        n *= int(d)
+    buf = _arena["buf"]
+    if buf is not None and (device is None or buf.device == torch.device(device)):
+        off = _arena["off"]
+        end = off + ((n + 31) & ~31)            # 128-byte aligned slices
+        if end <= buf.numel():
+            _arena["off"] = end
+            return buf[off:off + n].view(*shape)
+    return torch.zeros(*shape, device=device, dtype=torch.float32)
+
+
 def _rows_view(x: torch.Tensor):
     """(tensor, ld) such that x can be read as M rows of K elements with row stride ld (no copy when possible)."""
     K = x.shape[-1]
@@ -769,8 +796,8 @@ class _SetConvRbfFn(Function):
         sxk, sxq, B, Nk, Nq, C, p, unshared = ctx.cfg
         dout = _c(dout)
         # values that are data (context -> grid) need no dv: few-channel inputs then take the length-scale-only kernel
-        dv = torch.zeros_like(v) if (ctx.needs_input_grad[2] or C > 4) else None
-        dtheta = torch.zeros_like(theta)
+        dv = zeros(*v.shape, device=v.device) if (ctx.needs_input_grad[2] or C > 4) else None
+        dtheta = zeros(*theta.shape, device=v.device)
         LIB.call("npfk_setconv_bwd", _p(xk), sxk, _p(xq), sxq, _p(v), _p(theta), _p(out), _p(dout), C + 1, _p(dv),
                  _p(dtheta), B, Nk, Nq, C, p, unshared, _st())
         return None, None, dv, dtheta, None, None
@@ -817,10 +844,10 @@ class _SetConvInterpFn(Function):
         xk, xq, v, theta, wd, stats = ctx.saved_tensors
         sxk, sxq, B, Nk, Nq, C, p, unshared, has_bias = ctx.cfg
         dout = _c(dout)
-        dv = torch.zeros_like(v)
-        dtheta = torch.zeros_like(theta)
-        dwd = torch.zeros_like(wd)
-        dbias = torch.zeros_like(wd) if has_bias else None
+        dv = zeros(*v.shape, device=v.device)
+        dtheta = zeros(*theta.shape, device=v.device)
+        dwd = zeros(*wd.shape, device=v.device)
+        dbias = zeros(*wd.shape, device=v.device) if has_bias else None
         LIB.call("npfk_setconv_interp_bwd", _p(xk), sxk, _p(xq), sxq, _p(v), _p(theta), _p(wd), _p(stats), _p(dout),
                  _p(dv), _p(dwd), _p(dbias), _p(dtheta), B, Nk, Nq, C, p, unshared, _st())
         return None, None, dv, dtheta, dwd, dbias, None, None
@@ -922,7 +949,7 @@ class _NormActDwConvFn(Function):
         dev = x.device
         dh = torch.empty_like(x)
         # every "+=" output of the two kernels below comes out of one zero-filled buffer (one fill instead of five)
-        z = torch.zeros(C * (ks + 5), device=dev, dtype=torch.float32)
+        z = zeros(C * (ks + 5), device=dev)
         pg, pb, pw, pbias = ctx.params
         ng = ctx.needs_input_grad
         sinks = (_grad_sink(pg) if ng[1] else None, _grad_sink(pb) if ng[2] else None,

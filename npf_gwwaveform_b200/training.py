@@ -121,15 +121,26 @@ class FlatAdamTrainer:
             self._pending.append(dist.all_reduce(self.flat_grad[lo:hi], op=dist.ReduceOp.SUM, group=self.group,
                                                  async_op=True))
 
+    def _start_arena(self) -> None:
+        """one zero fill for every small "+=" buffer of the backward pass (kernels.zeros)"""
+        if getattr(self, "_zero_arena", None) is None:
+            self._zero_arena = torch.empty(1 << 21, device=self.flat_grad.device, dtype=torch.float32)      # 8 MB
+        self._zero_arena.zero_()
+        K.set_zero_arena(self._zero_arena)
+
     # ------------------------------------------------------------------ one optimisation step
     def step(self, batch: dict) -> torch.Tensor:
         """``batch`` holds X_cntxt, Y_cntxt, X_trgt, Y_trgt of this rank's shard; returns the local loss (device)."""
         self.flat_grad.zero_()
         self._fired.clear()
         self._pending.clear()
-        out = self.model(**batch)
-        loss = self.criterion(out, batch["Y_trgt"])
-        loss.backward()
+        self._start_arena()
+        try:
+            out = self.model(**batch)
+            loss = self.criterion(out, batch["Y_trgt"])
+            loss.backward()
+        finally:
+            K.set_zero_arena(None)
         for p_idx, p in enumerate(self.params):          # autograd may have replaced a .grad view (it must not)
             o, n = self.offsets[p_idx]
             if p.grad is None or p.grad.data_ptr() != self.flat_grad.data_ptr() + 4 * o:
@@ -279,6 +290,7 @@ class FlatAdamTrainer:
                     self.flat_grad.zero_()
                 if K.get_mode() == K.MODE_FAST:       # one rounding kernel for every weight of the step
                     K.set_tf32_flat(self.flat_param)
+                self._start_arena()
                 out = self.model(**self._static)
                 loss = self.criterion(out, self._static["Y_trgt"])
                 loss.backward()
@@ -300,6 +312,7 @@ class FlatAdamTrainer:
             K.set_direct_grad(False)
             K.set_sink_callback(None)
             K.set_tf32_flat(None)
+            K.set_zero_arena(None)
         self._losses[(zero, update)] = static_loss
         return graph
 
