@@ -257,6 +257,18 @@ def build_roofline(ksum, total_ms, args, pk, B, Nt, workload=None, steps=None):
             # peak = measured dense bf16 (MEASURED_PEAKS.json); the kernels run kind::tf32, whose dense peak is half
             e.update(achieved=tfs, peak=pk["tflops"], unit="TFLOP/s", frac=tfs / pk["tflops"],
                      frac_of_tf32_peak=tfs / (pk["tflops"] / 2), flops_per_launch=flops / calls)
+            if fam.startswith("attention"):
+                # head dim 16: a (query, key, head) pair is 64 tensor flop forward / 160 backward but also one ex2 and
+                # ~5 / ~8 CUDA-core instructions, so the SM's scalar pipes bound these kernels, not the tensor pipe
+                # (DESIGN.md section 3): pairs per clock per SM and the MUFU floor (16 ex2 / clk / SM) say how close they are
+                pairs = flops / (160.0 if "backward" in fam else 64.0)
+                clk = 1.965e9
+                e["per_pair"] = {"pairs_per_launch": pairs / calls,
+                                 "pairs_per_clk_per_sm": pairs / (ms * 1e-3) / (148 * clk),
+                                 "mufu_floor_ms": pairs / calls / (148 * 16 * clk) * 1e3,
+                                 "frac_of_mufu_floor": (pairs / calls / (148 * 16 * clk) * 1e3) / (ms / calls),
+                                 "note": "B200: 148 SMs x 16 ex2/clk at 1.965 GHz; FlashAttention-4 at head dim 128 runs at "
+                                         "~11 (forward) / ~2.9 (backward) pairs/clk/SM"}
         else:
             e.update(achieved=gbs, peak=pk["hbm_gbs"], unit="GB/s", frac=gbs / pk["hbm_gbs"],
                      algorithmic_bytes_per_launch=nbytes / calls, executed_tflops=tfs)

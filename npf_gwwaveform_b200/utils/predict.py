@@ -11,6 +11,7 @@ data source is overlapped as a DataLoader with pinned memory would be.
 """
 from __future__ import annotations
 
+import math
 from typing import Callable, Dict, Iterable, Iterator, Optional, Tuple
 
 import torch
@@ -44,7 +45,7 @@ def default_summary(p_yCc, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
         from ..losses import sum_log_prob
 
         lp = sum_log_prob(p_yCc, y)                                        # [n_z, B]
-        cols.append(torch.logsumexp(lp, 0) - torch.log(torch.tensor(float(lp.shape[0]), device=lp.device)))
+        cols.append(torch.logsumexp(lp, 0) - math.log(lp.shape[0]))
     return torch.stack(cols, dim=1)
 
 
@@ -57,12 +58,16 @@ def iter_chunks(tasks: Dict[str, torch.Tensor], lo: int, hi: int, chunk: int) ->
 
 def predict_sharded(model, tasks, n_tasks: Optional[int] = None, chunk: int = 64, rank: Optional[int] = None,
                     world_size: Optional[int] = None, reduce: Callable = default_summary,
-                    device: Optional[torch.device] = None) -> Tuple[torch.Tensor, Tuple[int, int]]:
+                    device: Optional[torch.device] = None, cuda_graph: bool = True) -> Tuple[torch.Tensor, Tuple[int, int]]:
     """Batched inference over this rank's shard of a task set.
 
     tasks: a dict of tensors ``X_cntxt[n,Nc,1], Y_cntxt[n,Nc,1], X_trgt[n,Nt,1]`` (optionally ``Y_trgt``), host or
            device; or a callable ``tasks(lo, hi) -> iterable of such dicts`` that yields the chunks of tasks [lo, hi)
            (a data source that synthesises / reads its shard itself; ``n_tasks`` is then required).
+    ``cuda_graph``: the forward + ``reduce`` of a chunk is captured into a CUDA graph the second time a chunk shape is
+    seen and replayed for every later chunk of that shape (the sweep is launch-bound otherwise: ~90 kernels for 4 ms of
+    work); chunks of any other shape (the shard's tail) run eagerly.  Models that draw random numbers per call (latent
+    paths) are not captured.
     Returns ``(summaries, (lo, hi))``: the ``reduce`` outputs of the shard's chunks concatenated along dim 0 (on the
     device), and the shard's task range.  Ranks do not exchange anything; gather the summaries yourself if you need them
     in one place (they are a few bytes per task).
@@ -107,6 +112,40 @@ def predict_sharded(model, tasks, n_tasks: Optional[int] = None, chunk: int = 64
             ev.record(copy)
         return dev, ev
 
+    latent = getattr(model, "encoded_path", "deterministic") != "deterministic"
+    # shapes -> (graph, static inputs, static output) once captured; None after the first eager pass.  Kept on the model
+    # so that later calls (the next shard, the next sweep) replay instead of capturing again; the graph reads the weights
+    # in place (and re-rounds them to tf32 on every replay), so it stays valid when they are updated
+    from .. import kernels as _K
+
+    cache = model.__dict__.setdefault("_npfk_predict_graphs", {})
+    graphs = cache.setdefault((id(reduce), _K.get_mode()), {})
+
+    def run(cur):
+        # as the reference predicts (visualize_1d.py:280-306): no Y_trgt, so latent models sample z from q(z|context)
+        p_yCc = model(cur["X_cntxt"], cur["Y_cntxt"], cur["X_trgt"])[0]
+        return reduce(p_yCc, cur)
+
+    def step(cur):
+        key = tuple((k, tuple(v.shape)) for k, v in sorted(cur.items()))
+        if not cuda_graph or latent:
+            return run(cur)
+        if key not in graphs:                       # first chunk of this shape: eager (also warms the kernels up)
+            graphs[key] = None
+            return run(cur)
+        if graphs[key] is None:                     # second chunk: capture, then replay for this and all later ones
+            static = {k: torch.empty_like(v) for k, v in cur.items()}
+            torch.cuda.synchronize(device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                out_static = run(static)
+            graphs[key] = (g, static, out_static)
+        g, static, out_static = graphs[key]
+        for k, v in cur.items():
+            static[k].copy_(v, non_blocking=True)
+        g.replay()
+        return out_static.clone()
+
     try:
         it = iter(chunks)
         nxt = next(it, None)
@@ -120,9 +159,7 @@ def predict_sharded(model, tasks, n_tasks: Optional[int] = None, chunk: int = 64
                     main.wait_event(ev)
                     for v in cur.values():
                         v.record_stream(main)
-                # as the reference predicts (visualize_1d.py:280-306): no Y_trgt, so latent models sample z from q(z|context)
-                p_yCc = model(cur["X_cntxt"], cur["Y_cntxt"], cur["X_trgt"])[0]
-                out.append(reduce(p_yCc, cur))
+                out.append(step(cur))
     finally:
         model.train(was_training)
     if not out:
