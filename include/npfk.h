@@ -211,6 +211,15 @@ int npfk_gather_rows(const float* src, const int64_t* idx, float* dst, int B, in
 int npfk_bn_stats(const float* x, int64_t rows, int C, double* scratch /* [2C + 1], see npfk_workspace_bytes */, float* stats,
                   float* running_mean, float* running_var, float momentum, int64_t* num_batches_tracked,
                   void* stream);
+/* npfk_bn_stats without caller scratch, for callers that cannot allocate.  No counterpart in the reference.
+ * Same arguments and results as npfk_bn_stats minus `scratch`; the [2C + 1]
+ * doubles live in a static __device__ array inside the library (64 KB + 256 B per GPU that loads it, held until
+ * exit).  C <= NPFK_BN_STATS_STATIC_MAX_C, else NPFK_ERR_INVALID with the limit in npfk_last_error().  Calls no
+ * cudaMalloc / cudaFree / allocating routine; every call clears and then shares the one array per GPU, so two calls
+ * that overlap on the same GPU (different streams, or graphs replayed concurrently) race: serialise them. */
+#define NPFK_BN_STATS_STATIC_MAX_C 4096
+int npfk_bn_stats_static(const float* x, int64_t rows, int C, float* stats, float* running_mean, float* running_var,
+                         float momentum, int64_t* num_batches_tracked, void* stream);
 /* y[b,l,c] = sum_j w[c,j] * h[b,l+j-ks/2,c] + bias[c] + res[b,l,c]   (zero padding of h outside [0,L))
  *   h = act((x - mean[c]) * gamma[c]*rsqrt(var[c]+eps) + beta[c]),  act = relu if `relu` else identity
  * mean == NULL: no normalisation (Normalization=nn.Identity).  mean/var are the batch statistics from

@@ -5,6 +5,8 @@
 // AvgPool1d / F.interpolate / cat glue of UnetCNN.apply_convs (cnn.py:451-490).  The reference permutes
 // NLC -> NCL around the CNN (cnn.py:363-375); here everything stays NLC so the channel index is the
 // coalesced one and the 1x1 convolutions are plain row-major Linear layers (npfk_linear_*).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace npfk {
@@ -447,6 +449,42 @@ inline unsigned ew_grid2(int64_t total, int block = 256) {
     return (unsigned)max((int64_t)1, min(g, (int64_t)kNumSMs * 16));
 }
 
+// ------------------------------------------------------------------------- npfk_bn_stats_static: scratch inside the library
+// For callers that cannot allocate (no cudaMalloc inside their loop, no torch): the [2C + 1] doubles bn_stats_kernel
+// accumulates into live in this file-scope array, 64 KB + 256 B per GPU that loads the library, held until exit.
+// On the host `g_bn_static_scratch` is only a handle for cudaGetSymbolAddress, never a device pointer: the address is
+// looked up once per device (with that device current) and that is what the kernel receives.
+constexpr int kBnStaticMaxC = 4096;
+constexpr int kBnStaticMaxDevices = 64;
+static __device__ __align__(256) double g_bn_static_scratch[2 * kBnStaticMaxC + 32];
+static double* g_bn_static_ptr[kBnStaticMaxDevices];      // device address per ordinal; written once, under the mutex
+static std::mutex g_bn_static_mutex;
+
+static int bn_static_scratch(double** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        set_error("bn_stats_static: cudaGetDevice: %s", cudaGetErrorString(e));
+        return NPFK_ERR_CUDA;
+    }
+    if (dev < 0 || dev >= kBnStaticMaxDevices) {
+        set_error("bn_stats_static: device ordinal %d outside [0, %d)", dev, kBnStaticMaxDevices);
+        return NPFK_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lock(g_bn_static_mutex);
+    if (!g_bn_static_ptr[dev]) {
+        double* ptr = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_bn_static_scratch);
+        if (e != cudaSuccess || !ptr) {
+            set_error("bn_stats_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+            return NPFK_ERR_CUDA;
+        }
+        g_bn_static_ptr[dev] = ptr;
+    }
+    *out = g_bn_static_ptr[dev];
+    return NPFK_OK;
+}
+
 }  // namespace npfk
 
 using namespace npfk;
@@ -470,6 +508,32 @@ int npfk_bn_stats(const float* x, int64_t rows, int C, double* scratch, float* s
     NPFK_LAUNCH(bn_stats_kernel, pgrid, 256, 0, st, x, rows, C, scratch, stats, running_mean, running_var, momentum,
                 reinterpret_cast<long long*>(num_batches_tracked));
     return check_launch("bn_stats");
+}
+
+int npfk_bn_stats_static(const float* x, int64_t rows, int C, float* stats, float* running_mean, float* running_var,
+                         float momentum, int64_t* num_batches_tracked, void* stream) {
+    NPFK_REQUIRE(x && stats, "bn_stats_static: null pointer");
+    NPFK_REQUIRE(rows > 0 && C > 0, "bn_stats_static: bad shape");
+    NPFK_REQUIRE(C <= kBnStaticMaxC,
+                 "bn_stats_static: C = %d exceeds the built-in scratch (NPFK_BN_STATS_STATIC_MAX_C = %d channels); "
+                 "use npfk_bn_stats with caller scratch", C, kBnStaticMaxC);
+    NPFK_REQUIRE((running_mean == nullptr) == (running_var == nullptr),
+                 "bn_stats_static: running stats must come in pairs");
+    double* scratch = nullptr;
+    const int rc = bn_static_scratch(&scratch);
+    if (rc != NPFK_OK) return rc;
+    cudaStream_t st = as_stream(stream);
+    // the array keeps the previous call's sums and ticket: both must start at zero
+    cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(double) * (2 * C + 1), st);
+    if (e != cudaSuccess) {
+        set_error("bn_stats_static: memset: %s", cudaGetErrorString(e));
+        return NPFK_ERR_CUDA;
+    }
+    dim3 pgrid((unsigned)ceil_div64(rows, kBnRows), (unsigned)((C + 127) / 128));
+    NPFK_REQUIRE(pgrid.x <= 2147483647u / pgrid.y, "bn_stats_static: grid too large");
+    NPFK_LAUNCH(bn_stats_kernel, pgrid, 256, 0, st, x, rows, C, scratch, stats, running_mean, running_var, momentum,
+                reinterpret_cast<long long*>(num_batches_tracked));
+    return check_launch("bn_stats_static");
 }
 
 int npfk_dwconv_fwd(const float* x, const float* mean, const float* var, const float* gamma, const float* beta,
