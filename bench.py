@@ -214,6 +214,8 @@ KERNEL_FAMILIES = {
     "decoder tail backward (log-likelihood + head dgrad/wgrad)": (["npfk_nll_head_bwd"], "hbm", "nll_head_bwd_kernel"),
     "linear forward (tcgen05 GEMM + bias/residual/ReLU epilogue)": (["npfk_linear_fwd"], "hbm", "tc_gemm_nt_kernel<0>"),
     "linear backward fused (dgrad + mask + wgrad)": (["npfk_linear_bwd_fused"], "hbm", "tc_linear_bwd_fused_kernel"),
+    "linear backward, two layers per launch (K1b: the gradient between them stays on chip)": (
+        ["npfk_linear_bwd_fused2"], "hbm", "tc_chain_bwd2_kernel"),
     "linear dgrad": (["npfk_linear_bwd_dx"], "hbm", "tc_gemm_nt_kernel<1>"),
     "linear wgrad": (["npfk_linear_bwd_dw"], "hbm", "tc_gemm_tn_kernel"),
     "residual + LayerNorm": (["npfk_add_layernorm_fwd", "npfk_add_layernorm_bwd"], "hbm", "add_layernorm_fwd"),

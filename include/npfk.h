@@ -70,6 +70,17 @@ int npfk_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx,
 int npfk_linear_bwd_fused(const float* g, int64_t ldg, const float* x, int64_t ldx, const float* w, int64_t ldw,
                           int masked, float* dx, int64_t lddx, float* dw, int64_t lddw, float* db, int64_t M, int N,
                           int K, int mode, void* stream);
+/* K1b: npfk_linear_bwd_fused for TWO consecutive 128 -> 128 layers in one kernel (NPFK_MODE_FAST arithmetic only).
+ * Upper layer (w1, saved input x1 = a ReLU output), lower layer (w0, saved input x0):
+ *   dw1 += g^T . x1 ; db1 += sum_m g ; gm = (g . w1) masked by (x1 > 0), rounded to tf32, kept on chip
+ *   dw0 += gm^T . x0 ; db0 += sum_m gm ; dx = (gm . w0) [masked by (x0 > 0) when flags & NPFK_BWD_MASKED]
+ * flags & NPFK_BWD_DX_ACCUMULATE: dx += (TMA reduce-add).  db1 / db0 may be NULL.  Per 128 rows the kernel reads g, x1,
+ * x0 and writes dx: four activation-sized tensors for two layers instead of six (autograd of mlp.py:95-109).
+ * All matrices [*, 128] fp32; returns NPFK_ERR_UNSUPPORTED for M < 128 or unaligned operands. */
+int npfk_linear_bwd_fused2(const float* g, int64_t ldg, const float* x1, int64_t ldx1, const float* w1, int64_t ldw1,
+                           const float* x0, int64_t ldx0, const float* w0, int64_t ldw0, int flags, float* dx,
+                           int64_t lddx, float* dw1, int64_t lddw1, float* db1, float* dw0, int64_t lddw0, float* db0,
+                           int64_t M, void* stream);
 /* ---- K1: a ReLU-MLP chain of L <= 8 layers of 128 -> 128 as ONE kernel (NPFK_MODE_FAST only) ---------------
  * Replaces MLP.forward (npf/architectures/mlp.py:95-109), the sum-merge of MergeFlatInputs
  * (npf/architectures/encoders.py:175-183) and, with the tail, decode + sum_log_prob

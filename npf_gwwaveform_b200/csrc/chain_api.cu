@@ -12,6 +12,13 @@ int tc_mlp_chain_fwd(const float* x, int64_t ldx, int64_t M, int L, const float*
                      int relu_mask, int res_layer, const float* res, int64_t ldres, int64_t res_rows, float* const* out,
                      const float* head_w, const float* head_b, float* suff, const float* y, int64_t y_rows, int64_t T,
                      float* sum_lp, cudaStream_t st);
+bool chain_bwd2_eligible(const float* g, int64_t ldg, const float* h1, int64_t ldh1, const float* w1, int64_t ldw1,
+                         const float* h0, int64_t ldh0, const float* w0, int64_t ldw0, const float* dx, int64_t lddx,
+                         const float* dw1, int64_t lddw1, const float* dw0, int64_t lddw0, int64_t M);
+int tc_chain_bwd2(const float* g, int64_t ldg, const float* h1, int64_t ldh1, const float* w1, int64_t ldw1,
+                  const float* h0, int64_t ldh0, const float* w0, int64_t ldw0, int flags, float* dx, int64_t lddx,
+                  float* dw1, int64_t lddw1, float* db1, float* dw0, int64_t lddw0, float* db0, int64_t M,
+                  cudaStream_t st);
 }
 
 // One warp per row at a time, a lane owns 4 consecutive columns (16-byte loads / stores); the head's weight and bias
@@ -141,6 +148,23 @@ int npfk_nll_head_bwd(const float* h, int64_t ldh, const float* head_w, const fl
 }
 
 /* bytes of caller-provided workspace an op needs for the given sizes (0 = none); SURVEY.md section 8b */
+int npfk_linear_bwd_fused2(const float* g, int64_t ldg, const float* x1, int64_t ldx1, const float* w1, int64_t ldw1,
+                           const float* x0, int64_t ldx0, const float* w0, int64_t ldw0, int flags, float* dx,
+                           int64_t lddx, float* dw1, int64_t lddw1, float* db1, float* dw0, int64_t lddw0, float* db0,
+                           int64_t M, void* stream) {
+    using namespace npfk;
+    NPFK_REQUIRE(g && x1 && w1 && x0 && w0 && dx && dw1 && dw0, "linear_bwd_fused2: null pointer");
+    NPFK_REQUIRE((flags & ~3) == 0, "linear_bwd_fused2: unknown flag bits %d", flags);
+    if (M <= 0) return NPFK_OK;
+    if (!tc::chain_bwd2_eligible(g, ldg, x1, ldx1, w1, ldw1, x0, ldx0, w0, ldw0, dx, lddx, dw1, lddw1, dw0, lddw0, M)) {
+        set_error("linear_bwd_fused2: needs M >= 128, 16-byte aligned operands and row pitches that are multiples of 4 "
+                  "floats (got M=%lld); run the two layers through npfk_linear_bwd_fused", (long long)M);
+        return NPFK_ERR_UNSUPPORTED;
+    }
+    return tc::tc_chain_bwd2(g, ldg, x1, ldx1, w1, ldw1, x0, ldx0, w0, ldw0, flags, dx, lddx, dw1, lddw1, db1, dw0, lddw0,
+                             db0, M, as_stream(stream));
+}
+
 int64_t npfk_workspace_bytes(int op, int64_t d0, int64_t d1, int64_t d2) {
     switch (op) {
         case NPFK_OP_MHA_BWD: return 4 * npfk_mha_bwd_ws_floats((int)d0, d1, (int)d2);   // (B, Nq, H)

@@ -357,6 +357,12 @@ def set_chain_fusion(flag: bool) -> None:
     _state["chain_fusion"] = bool(flag)
 
 
+def set_chain_bwd_fusion(flag: bool) -> None:
+    """Developer switch for A/B timing: False back-propagates every layer through its own npfk_linear_bwd_fused launch
+    instead of pairing 128 -> 128 layers in npfk_linear_bwd_fused2 (K1b)."""
+    _state["chain_bwd_fusion"] = bool(flag)
+
+
 def _ptr_array(ts):
     return (ctypes.c_void_p * len(ts))(*[None if t is None else t.data_ptr() for t in ts])
 
@@ -527,25 +533,39 @@ class _MlpChainFn(Function):
                 dres = torch.empty(res_shape, device=g.device, dtype=torch.float32)
                 LIB.call("npfk_rows_fold_sum", _p(g), N_out, _p(dres), N_out, res_rows, M // res_rows, N_out, st)
         grads_wb = [None] * (2 * n_layers)
-        for i in range(n_layers - 1, -1, -1):
+
+        def need_w_of(i):
+            return ctx.needs_input_grad[7 + 2 * i] or (has_b[i] and ctx.needs_input_grad[8 + 2 * i])
+
+        def wgrad_buffers(i):
+            """(dw, db) of layer i: the trainer's flat gradient buffer when it takes direct writes, else fresh zeros that are
+            handed back to autograd"""
+            N, Kd = dims[i][0], dims[i][1]
+            sink_w = _grad_sink(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[7 + 2 * i] else None
+            sink_b = _grad_sink(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[8 + 2 * i] else None
+            dw = sink_w if sink_w is not None else torch.zeros(N, Kd, device=dev, dtype=torch.float32)
+            db = None
+            if has_b[i]:
+                db = sink_b if sink_b is not None else torch.zeros(N, device=dev, dtype=torch.float32)
+            grads_wb[2 * i] = None if sink_w is not None else dw
+            grads_wb[2 * i + 1] = None if sink_b is not None else db
+            return dw, db
+
+        def square(i):
+            return dims[i][0] == _CHAIN_DIM and dims[i][1] == _CHAIN_DIM and dims[i][3] == _CHAIN_DIM
+
+        pair_ok = (mode == MODE_FAST and _state.get("chain_bwd_fusion", True) and M >= 128)
+        i = n_layers - 1
+        while i >= 0:
             N, Kd, ldh, ldw, _ = dims[i]
             hin = acts[i]
-            need_w = ctx.needs_input_grad[7 + 2 * i] or (has_b[i] and ctx.needs_input_grad[8 + 2 * i])
+            need_w = need_w_of(i)
             need_dx = i > 0 or ctx.needs_input_grad[5]
             masked = i > 0 or x_is_relu
-            dw = db = None
-            if need_w:
-                sink_w = _grad_sink(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[7 + 2 * i] else None
-                sink_b = _grad_sink(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[8 + 2 * i] else None
-                dw = sink_w if sink_w is not None else torch.zeros(N, Kd, device=dev, dtype=torch.float32)
-                db = None
-                if has_b[i]:
-                    db = sink_b if sink_b is not None else torch.zeros(N, device=dev, dtype=torch.float32)
-                grads_wb[2 * i] = None if sink_w is not None else dw
-                grads_wb[2 * i + 1] = None if sink_b is not None else db
             if head_fused and i == n_layers - 1 and M > 0:
                 # decoder tail: d(log-likelihood)/d(suff), the head's dgrad (+ ReLU mask of the layer below) and its
                 # weight / bias gradients in one pass over the last hidden activation
+                dw, db = wgrad_buffers(i) if need_w else (None, None)
                 dx = torch.empty(M, Kd, device=dev, dtype=torch.float32) if need_dx else None
                 yv, T = nll_saved if nll_saved is not None else (None, 0)
                 use_lp = dsum_lp is not None and yv is not None
@@ -555,13 +575,32 @@ class _MlpChainFn(Function):
                 g = dx
                 if not need_dx:
                     break
+                i -= 1
                 continue
+            # K1b: two consecutive 128 -> 128 layers in one kernel -- the gradient between them stays on the SM
+            if (pair_ok and i >= 1 and square(i) and square(i - 1) and need_w and need_w_of(i - 1)
+                    and (i - 1 > 0 or ctx.needs_input_grad[5]) and ldh % 4 == 0 and dims[i - 1][2] % 4 == 0
+                    and hin.data_ptr() % 16 == 0 and acts[i - 1].data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0):
+                dw1, db1 = wgrad_buffers(i)
+                dw0, db0 = wgrad_buffers(i - 1)
+                masked0 = (i - 1 > 0) or x_is_relu
+                dx = torch.empty(M, _CHAIN_DIM, device=dev, dtype=torch.float32)
+                LIB.call("npfk_linear_bwd_fused2", _p(g), N, _p(hin), ldh, _p(wvs[i]), ldw, _p(acts[i - 1]), dims[i - 1][2],
+                         _p(wvs[i - 1]), dims[i - 1][3], int(masked0), _p(dx), _CHAIN_DIM, _p(dw1), _CHAIN_DIM, _p(db1),
+                         _p(dw0), _CHAIN_DIM, _p(db0), M, st)
+                g = dx
+                i -= 2
+                continue
+            dw = db = None
+            if need_w:
+                dw, db = wgrad_buffers(i)
             if need_w and need_dx and M > 0:
                 # one pass over g and the saved input: dgrad (+ ReLU mask from hin) and wgrad together
                 dx = torch.empty(M, Kd, device=dev, dtype=torch.float32)
                 LIB.call("npfk_linear_bwd_fused", _p(g), N, _p(hin), ldh, _p(wvs[i]), ldw, int(masked), _p(dx), Kd,
                          _p(dw), Kd, _p(db), M, N, Kd, mode, st)
                 g = dx
+                i -= 1
                 continue
             if need_w and M > 0:
                 LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(hin), ldh, _p(dw), Kd, _p(db), M, N, Kd, mode, st)
@@ -573,6 +612,7 @@ class _MlpChainFn(Function):
                 LIB.call("npfk_linear_bwd_dx", _p(g), N, _p(wvs[i]), ldw, _p(hin) if masked else None, ldh if masked else 0,
                          _p(dx), Kd, M, N, Kd, mode, st)
             g = dx
+            i -= 1
         dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[5]) else None
         return (None, None, None, None, None, dx, dres, *grads_wb)
 
@@ -1259,6 +1299,9 @@ class KernelTimer:
         if name == "npfk_linear_bwd_fused":
             M, N, Kd = a[12], a[13], a[14]
             return 4.0 * M * N * Kd, 4.0 * (M * N + 2 * M * Kd)
+        if name == "npfk_linear_bwd_fused2":
+            M = a[19]       # g, x1, x0 read, dx written: four [M,128] tensors; two dgrads + two wgrads
+            return 8.0 * M * 128 * 128, 4.0 * 4 * M * 128
         if name == "npfk_mlp_chain_fwd":
             # algorithmic HBM bytes: the input tile, the residual, every activation the caller asked for, the head's [M,2]
             M, L = a[2], a[3]

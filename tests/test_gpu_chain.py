@@ -171,3 +171,86 @@ def test_decoder_tail_head_and_loglik(Z, B, T, L):
     unfused = [xs3.grad] + [t.grad for wb in layers for t in wb]
     for a, b in zip(fused, unfused):
         assert rel(a, b) < 2e-4, (a.shape, rel(a, b))
+
+
+# ------------------------------------------------------------------------------------------ K1b: two layers per backward launch
+@pytest.mark.parametrize("M,L,x_is_relu,with_res", [
+    (128, 2, True, False), (300, 2, False, True), (128 * 148 + 77, 3, True, False), (1000, 4, False, True),
+    (4096, 5, True, False), (256, 8, False, False),
+])
+def test_chain_backward_pairs_match_layerwise(M, L, x_is_relu, with_res):
+    """npfk_linear_bwd_fused2 (K1b, csrc/tc_chain_bwd.cu) against one npfk_linear_bwd_fused launch per layer: both issue the
+    same tcgen05 k-steps on the same operands (the gradient between the two layers is rounded to tf32 in either path), so
+    dx agrees bit for bit; the weight / bias gradients are sums over CTAs in a different order.  Autograd of
+    mlp.py:95-109."""
+    from npf_gwwaveform_b200 import kernels as Kn
+
+    g = torch.Generator().manual_seed(7 * M + L)
+    x = torch.randn(M, 128, generator=g)
+    x = (torch.relu(x) if x_is_relu else x).cuda()
+    res = torch.randn(M, 128, generator=g).cuda() if with_res else None
+    dy = torch.randn(M, 128, generator=g).cuda()
+    got, launches = [], []
+    for paired in (True, False):
+        Kn.set_chain_bwd_fusion(paired)
+        try:
+            layers = _layers(L, 5 + L)
+            for w, _ in layers:
+                Kn.tf32_weight(w)
+            xs = x.clone().requires_grad_(True)
+            rs = res.clone().requires_grad_(True) if with_res else None
+            y = Kn.mlp_chain(xs, layers, res=rs, out_relu=with_res, x_is_relu=x_is_relu)
+            n0 = Kn.launch_count()
+            y.backward(dy)
+            launches.append(Kn.launch_count() - n0)
+        finally:
+            Kn.set_chain_bwd_fusion(True)
+        got.append([xs.grad] + [t.grad for wb in layers for t in wb] + ([rs.grad] if with_res else []))
+    # L layers: floor(L / 2) pair launches + (L % 2) single ones, against L (+ the ReLU backward of the output)
+    assert launches[1] - launches[0] == L // 2, launches
+    assert torch.equal(got[0][0], got[1][0]), float((got[0][0] - got[1][0]).abs().max())
+    for a, b in zip(got[0][1:], got[1][1:]):
+        assert float((a - b).abs().max() / b.abs().max()) < 1e-5
+
+
+@pytest.mark.parametrize("M,masked0,with_db,accumulate", [
+    (128, True, True, False), (300, False, True, False), (128 * 148 * 2 + 77, True, False, False), (4096, True, True, True),
+])
+def test_linear_bwd_fused2_c_abi_against_float64(M, masked0, with_db, accumulate):
+    """the entry point itself, raw pointers: every output against the float64 definition in include/npfk.h"""
+    import ctypes
+
+    from npf_gwwaveform_b200 import kernels as Kn
+    from npf_gwwaveform_b200._lib import LIB
+
+    def ptr(t):
+        return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+    g = torch.Generator().manual_seed(M)
+    G = torch.randn(M, 128, generator=g).cuda()
+    H1 = torch.relu(torch.randn(M, 128, generator=g)).cuda()
+    H0 = torch.relu(torch.randn(M, 128, generator=g)).cuda()
+    W1 = Kn.tf32_weight(torch.randn(128, 128, generator=g).cuda() / 11)
+    W0 = Kn.tf32_weight(torch.randn(128, 128, generator=g).cuda() / 11)
+    dx0 = torch.randn(M, 128, generator=g).cuda() if accumulate else None
+    dx = dx0.clone() if accumulate else torch.empty(M, 128, device="cuda")
+    dw1, dw0 = torch.zeros(128, 128, device="cuda"), torch.zeros(128, 128, device="cuda")
+    db1 = torch.zeros(128, device="cuda") if with_db else None
+    db0 = torch.zeros(128, device="cuda") if with_db else None
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    LIB.call("npfk_linear_bwd_fused2", ptr(G), 128, ptr(H1), 128, ptr(W1), 128, ptr(H0), 128, ptr(W0), 128,
+             int(masked0) | (2 if accumulate else 0), ptr(dx), 128, ptr(dw1), 128, ptr(db1), ptr(dw0), 128, ptr(db0), M, st)
+    torch.cuda.synchronize()
+    Gd, H1d, H0d, W1d, W0d = (t.double().cpu() for t in (G, H1, H0, W1, W0))
+    gm = (Gd @ W1d) * (H1d > 0)
+    ref_dx = gm @ W0d
+    if masked0:
+        ref_dx = ref_dx * (H0d > 0)
+    if accumulate:
+        ref_dx = ref_dx + dx0.double().cpu()
+    checks = [(dx, ref_dx), (dw1, Gd.T @ H1d), (dw0, gm.T @ H0d)]
+    if with_db:
+        checks += [(db1, Gd.sum(0)), (db0, gm.sum(0))]
+    for got, ref in checks:
+        err = float((got.double().cpu() - ref).abs().max() / ref.abs().max())
+        assert err < 3e-3, err      # tf32 operands (2^-11 each), fp32 accumulate
