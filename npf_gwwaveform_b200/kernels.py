@@ -537,12 +537,17 @@ class _MlpChainFn(Function):
         def need_w_of(i):
             return ctx.needs_input_grad[7 + 2 * i] or (has_b[i] and ctx.needs_input_grad[8 + 2 * i])
 
+        sunk = []       # parameters whose gradients the next launch writes straight into the trainer's flat buffer
+
         def wgrad_buffers(i):
             """(dw, db) of layer i: the trainer's flat gradient buffer when it takes direct writes, else fresh zeros that are
-            handed back to autograd"""
+            handed back to autograd.  The sink callbacks fire in ``launched()``, AFTER the kernel that writes the gradients
+            is enqueued: a pair launch (K1b) covers four parameters, and a callback that ran before the launch could make
+            the trainer all-reduce a bucket that ends inside the pair before its gradients exist."""
             N, Kd = dims[i][0], dims[i][1]
-            sink_w = _grad_sink(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[7 + 2 * i] else None
-            sink_b = _grad_sink(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[8 + 2 * i] else None
+            sink_w = _grad_sink_buf(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[7 + 2 * i] else None
+            sink_b = _grad_sink_buf(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[8 + 2 * i] else None
+            sunk.extend(prm for prm, buf in ((ctx.wb[2 * i], sink_w), (ctx.wb[2 * i + 1], sink_b)) if buf is not None)
             dw = sink_w if sink_w is not None else torch.zeros(N, Kd, device=dev, dtype=torch.float32)
             db = None
             if has_b[i]:
@@ -550,6 +555,13 @@ class _MlpChainFn(Function):
             grads_wb[2 * i] = None if sink_w is not None else dw
             grads_wb[2 * i + 1] = None if sink_b is not None else db
             return dw, db
+
+        def launched():
+            cb = _state.get("sink_cb")
+            if cb is not None:
+                for prm in sunk:
+                    cb(prm)
+            sunk.clear()
 
         def square(i):
             return dims[i][0] == _CHAIN_DIM and dims[i][1] == _CHAIN_DIM and dims[i][3] == _CHAIN_DIM
@@ -572,6 +584,7 @@ class _MlpChainFn(Function):
                 LIB.call("npfk_nll_head_bwd", _p(hin), ldh, _p(wvs[i]), _p(y_out), _p(y_nll if use_lp else None),
                          y_nll.numel() if use_lp else 0, T if use_lp else 0,
                          _p(_c(dsum_lp).reshape(-1)) if use_lp else None, _p(g), int(masked), _p(dx), _p(dw), _p(db), M, st)
+                launched()
                 g = dx
                 if not need_dx:
                     break
@@ -588,6 +601,7 @@ class _MlpChainFn(Function):
                 LIB.call("npfk_linear_bwd_fused2", _p(g), N, _p(hin), ldh, _p(wvs[i]), ldw, _p(acts[i - 1]), dims[i - 1][2],
                          _p(wvs[i - 1]), dims[i - 1][3], int(masked0), _p(dx), _CHAIN_DIM, _p(dw1), _CHAIN_DIM, _p(db1),
                          _p(dw0), _CHAIN_DIM, _p(db0), M, st)
+                launched()
                 g = dx
                 i -= 2
                 continue
@@ -599,11 +613,13 @@ class _MlpChainFn(Function):
                 dx = torch.empty(M, Kd, device=dev, dtype=torch.float32)
                 LIB.call("npfk_linear_bwd_fused", _p(g), N, _p(hin), ldh, _p(wvs[i]), ldw, int(masked), _p(dx), Kd,
                          _p(dw), Kd, _p(db), M, N, Kd, mode, st)
+                launched()
                 g = dx
                 i -= 1
                 continue
             if need_w and M > 0:
                 LIB.call("npfk_linear_bwd_dw", _p(g), N, _p(hin), ldh, _p(dw), Kd, _p(db), M, N, Kd, mode, st)
+            launched()
             if not need_dx:
                 g = None
                 break
