@@ -22,14 +22,16 @@ for _ in range(2):
     o.backward(do)
     q.grad = k.grad = v.grad = None
 del o
-# MLP chain on the target rows: forward GEMMs, fused backward (dgrad + mask + wgrad), first-layer wgrad
+# MLP chain on the target rows: fused forward chain (K1), backward as one pair launch (K1b: layers 3 + 2) and one
+# single-layer fused launch (layer 1: dgrad + mask + wgrad)
 x = q.detach().reshape(B * Nq, E).requires_grad_(True)
 w1 = (torch.randn(128, 128, device="cuda") * 0.05).requires_grad_(True)
 w2 = (torch.randn(128, 128, device="cuda") * 0.05).requires_grad_(True)
+w3 = (torch.randn(128, 128, device="cuda") * 0.05).requires_grad_(True)
 b1 = torch.zeros(128, device="cuda", requires_grad=True)
 dy = do.reshape(B * Nq, E)
 for _ in range(2):
-    y = Kn.mlp_chain(x, [(w1, b1), (w2, b1)])
+    y = Kn.mlp_chain(x, [(w1, b1), (w2, b1), (w3, b1)])
     y.backward(dy)
     x.grad = None
 del y
