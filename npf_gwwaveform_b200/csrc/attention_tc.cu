@@ -177,55 +177,87 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 for (int c = 0; c < nc; ++c)
                     if (!mbar_wait(&bar.kv_full[c], 0, cta_abort, p.g_abort, 24)) return;
                 tc_fence_after();
-                uint32_t n_steps[3] = {0, 0, 0}, s_issued[3] = {0, 0, 0}, pv_done[3] = {0, 0, 0};
-                for (int g = 0; g < nwg; ++g) n_steps[g] = (uint32_t)((U - g + nwg - 1) / nwg) * (uint32_t)nc;
-                auto issue_s = [&](int g, uint32_t n) -> bool {
-                    const int k = (int)(n / (uint32_t)nc), c = (int)(n % (uint32_t)nc);
-                    const int u = nwg * k + g, t = u / HB, hb = u % HB;
-                    const uint32_t qs = (uint32_t)t % kAQSlots;
+                // Per-stream state.  Every loop over the streams is fully unrolled, so these arrays live in registers and
+                // the (unit, chunk) of the next step is carried along instead of being divided out of a step counter: the
+                // instruction latency of this one thread is on the critical path of all three warpgroups.
+                uint32_t n_steps[3], s_n[3], p_n[3];     // steps in all, S issued, P.V issued
+                int s_u[3], s_c[3], p_u[3], p_c[3];      // unit / chunk of the next S and of the next P.V
+#pragma unroll
+                for (int g = 0; g < 3; ++g) {
+                    n_steps[g] = g < nwg ? (uint32_t)((U - g + nwg - 1) / nwg) * (uint32_t)nc : 0u;
+                    s_n[g] = p_n[g] = 0u;
+                    s_u[g] = p_u[g] = g;
+                    s_c[g] = p_c[g] = 0;
+                }
+                // S of the next step of stream g.  Returns 1 = issued, 0 = not now, -1 = the CTA is aborting.  When the unit's
+                // Q tile has not landed, waiting for it is safe only if its load no longer depends on this thread: the
+                // slot's previous tile (t - kAQSlots) is released by the last P.V of BOTH of its heads, which belong to other
+                // streams -- a stream that has run ahead must keep serving the others instead of blocking (deadlock).
+                auto issue_s = [&](const int g) -> int {
+                    const int u = s_u[g], c = s_c[g], t = u / HB, hb = u % HB;
+                    const uint32_t qs = (uint32_t)t % kAQSlots, qph = ((uint32_t)t / kAQSlots) & 1;
                     if (c == 0) {
-                        if (!mbar_wait(&bar.q_full[qs], ((uint32_t)t / kAQSlots) & 1, cta_abort, p.g_abort, 23)) return false;
+                        if (t >= kAQSlots && !mbar_test_wait(smem_u32(&bar.q_full[qs]), qph)) {
+                            const int u_last = (t - kAQSlots) * HB + HB - 1;      // every unit up to here must be finished
+                            bool released = true;
+#pragma unroll
+                            for (int g2 = 0; g2 < 3; ++g2) released &= (g2 >= nwg) | (p_u[g2] > u_last);
+                            if (!released) return 0;
+                        }
+                        if (!mbar_wait(&bar.q_full[qs], qph, cta_abort, p.g_abort, 23)) return -1;
                         tc_fence_after();
                     }
-                    const uint32_t ko = (uint32_t)(hb * D * 4);
+                    const uint32_t ko = (uint32_t)(hb * D * 4), sb = s_n[g] & 1;
                     const uint64_t dq = sdesc_advance(d_q0, qs * kAQBytes + ko);
                     const uint64_t dk = sdesc_advance(d_ring_k, (uint32_t)c * kASlotBytes + ko);
-                    const uint32_t tS = tmem_base + (uint32_t)g * tm_wg + (n & 1) * kAKC;
+                    const uint32_t tS = tmem_base + (uint32_t)g * tm_wg + sb * kAKC;
 #pragma unroll
                     for (int s = 0; s < D / 8; ++s)
                         umma_tf32(tS, sdesc_advance(dq, s * 32), sdesc_advance(dk, s * 32), idesc_s, s > 0);
-                    umma_commit(&bar.s_full[g * 2 + (n & 1)]);
-                    return true;
+                    umma_commit(&bar.s_full[g * 2 + sb]);
+                    ++s_n[g];
+                    if (++s_c[g] == nc) {
+                        s_c[g] = 0;
+                        s_u[g] += nwg;
+                    }
+                    return 1;
                 };
-                for (int g = 0; g < nwg; ++g)
+#pragma unroll
+                for (int g = 0; g < 3; ++g)
+#pragma unroll
                     for (int i = 0; i < 2; ++i)
-                        if (s_issued[g] < n_steps[g]) {
-                            if (!issue_s(g, s_issued[g])) return;
-                            ++s_issued[g];
-                        }
+                        if (s_n[g] < n_steps[g] && issue_s(g) < 0) return;       // the first tiles never wait for a slot
                 uint32_t spin = 0;
-                while (pv_done[0] < n_steps[0] || pv_done[1] < n_steps[1] || pv_done[2] < n_steps[2]) {
+                while (p_n[0] < n_steps[0] || p_n[1] < n_steps[1] || p_n[2] < n_steps[2]) {
                     bool progressed = false;
-                    for (int g = 0; g < nwg; ++g) {
-                        const uint32_t n = pv_done[g];
+#pragma unroll
+                    for (int g = 0; g < 3; ++g) {
+                        const uint32_t n = p_n[g];
                         if (n >= n_steps[g]) continue;
-                        if (!mbar_try_wait(smem_u32(&bar.p_ready[g * 2 + (n & 1)]), (n >> 1) & 1)) continue;
+                        if (s_n[g] < n_steps[g] && s_n[g] < n + 2) {      // an S issue was put off: retry
+                            const int r = issue_s(g);
+                            if (r < 0) return;
+                            progressed |= r > 0;
+                        }
+                        if (n >= s_n[g]) continue;
+                        const uint32_t sb = n & 1;
+                        if (!mbar_try_wait(smem_u32(&bar.p_ready[g * 2 + sb]), (n >> 1) & 1)) continue;
                         tc_fence_after();
-                        const int k = (int)(n / (uint32_t)nc), c = (int)(n % (uint32_t)nc);
-                        const int u = nwg * k + g, t = u / HB, hb = u % HB;
-                        const uint32_t tP = tmem_base + (uint32_t)g * tm_wg + (n & 1) * kAKC;
-                        const uint32_t tO = tmem_base + (uint32_t)g * tm_wg + kATmemO + (n & 1) * o_str;
+                        const int u = p_u[g], c = p_c[g], t = u / HB, hb = u % HB;
+                        const uint32_t tP = tmem_base + (uint32_t)g * tm_wg + sb * kAKC;
+                        const uint32_t tO = tmem_base + (uint32_t)g * tm_wg + kATmemO + sb * o_str;
                         const uint64_t dv = sdesc_advance(d_ring_v, (uint32_t)c * kASlotBytes + ((D == 16) ? (uint32_t)hb * 64u : 0u));
 #pragma unroll
                         for (int j = 0; j < kAKC / 8; ++j)
                             umma_tf32_ts(tO, tP + 8 * j, sdesc_advance(dv, j * 1024), idesc_pv, j > 0);
-                        umma_commit(&bar.o_full[g * 2 + (n & 1)]);
-                        if (c == nc - 1) umma_commit(&bar.q_empty[(uint32_t)t % kAQSlots]);
-                        ++pv_done[g];
-                        if (s_issued[g] < n_steps[g]) {
-                            if (!issue_s(g, s_issued[g])) return;
-                            ++s_issued[g];
+                        umma_commit(&bar.o_full[g * 2 + sb]);
+                        ++p_n[g];
+                        if (++p_c[g] == nc) {
+                            umma_commit(&bar.q_empty[(uint32_t)t % kAQSlots]);
+                            p_c[g] = 0;
+                            p_u[g] += nwg;
                         }
+                        if (s_n[g] < n_steps[g] && issue_s(g) < 0) return;
                         progressed = true;
                     }
                     if (progressed) {

@@ -45,6 +45,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar_addr, uint32_t parity
         : "memory");
     return ok != 0;
 }
+// Immediate test (mbarrier.test_wait): unlike try_wait, which may suspend the thread for a hardware time slice when the
+// phase is not complete, this returns at once -- for threads that poll SEVERAL barriers in turn.
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar_addr, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(bar_addr), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 // Bounded wait; returns false when the CTA is aborting.  `code` identifies the waiting site.
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, volatile int* cta_abort, int* g_abort, int code) {
     const uint32_t addr = smem_u32(bar);
