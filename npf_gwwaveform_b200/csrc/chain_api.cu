@@ -21,7 +21,7 @@ int tc_chain_bwd2(const float* g, int64_t ldg, const float* h1, int64_t ldh1, co
                   cudaStream_t st);
 }
 
-// One warp per row at a time, a lane owns 4 consecutive columns (16-byte loads / stores); the head's weight and bias
+// A warp per 32 rows at a time, a lane owns 4 consecutive columns (16-byte loads / stores); the head's weight and bias
 // gradients are accumulated in registers over all rows of the warp, reduced across the block's warps in shared memory
 // and added to HBM with one atomic per (block, element).
 constexpr int kHbWarps = 8;
@@ -36,62 +36,59 @@ nll_head_bwd_kernel(const float* __restrict__ h, int64_t ldh, const float* __res
     const float4 w1 = __ldg(reinterpret_cast<const float4*>(head_w + 128) + lane);
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
     float b0 = 0.f, b1 = 0.f;
-    const int64_t wstride = (int64_t)gridDim.x * kHbWarps;
-    constexpr int U = 4;       // rows in flight per warp: their loads are issued together (the kernel is latency-bound otherwise)
-    for (int64_t row0 = (int64_t)blockIdx.x * kHbWarps + warp; row0 < M; row0 += wstride * U) {
-        float4 hv[U];
-        float2 sf[U], di[U];
-        float gl[U], yv[U];
-        bool okr[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int64_t row = row0 + u * wstride;
-            okr[u] = row < M;
-            const int64_t rr = okr[u] ? row : row0;
-            hv[u] = __ldg(reinterpret_cast<const float4*>(h + rr * ldh) + lane);
-            sf[u] = __ldg(reinterpret_cast<const float2*>(suff) + rr);
-            // M, T, y_rows < 2^31 (checked by the entry point): 32-bit division
-            gl[u] = dsum_lp ? __ldg(dsum_lp + (uint32_t)rr / (uint32_t)T) : 0.f;
-            yv[u] = dsum_lp ? __ldg(y + (uint32_t)rr % (uint32_t)y_rows) : 0.f;
-            di[u] = dsuff_in ? __ldg(reinterpret_cast<const float2*>(dsuff_in) + rr) : make_float2(0.f, 0.f);
-        }
-        // the per-row scalars (softplus / sigmoid / reciprocal) are evaluated by ONE lane per row (lane u for row u) and
-        // broadcast: all 32 lanes doing the same transcendental work made the kernel XU-bound (ncu: xu 29 %, 60 % of HBM)
+    // A warp takes 32 consecutive rows per iteration.  Phase 1, lane = row: the per-row scalars (d lp / d suff: softplus,
+    // sigmoid, reciprocal, the task index) are computed ONCE per row by the lane that owns it, all lanes busy -- as a
+    // "one lane computes, the others wait" branch per row they cost the warp ~100 issue slots per row and made the kernel
+    // issue-bound at 60 % of HBM.  Phase 2, lane = 4 columns: the scalars of row r are broadcast with two shuffles, the rows'
+    // 512-byte loads are issued four at a time.
+    const int64_t nwarps = (int64_t)gridDim.x * kHbWarps;
+    for (int64_t base = ((int64_t)blockIdx.x * kHbWarps + warp) * 32; base < M; base += nwarps * 32) {
+        const int64_t row = base + lane;
         float my0 = 0.f, my1 = 0.f;
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            if (lane == u) {
-                my0 = di[u].x;
-                my1 = di[u].y;
-                if (dsum_lp) {
-                    // lp = -(y - mu)^2 / (2 s^2) - log s - c,  s = 0.01 + 0.99 softplus(raw):  d lp/d mu = d / s^2,
-                    // d lp/d raw = (d^2 / s^3 - 1 / s) * 0.99 sigmoid(raw)
-                    const float sc = 0.01f + 0.99f * softplus_f(sf[u].y), inv = 1.f / sc;
-                    const float d = yv[u] - sf[u].x;
-                    my0 = fmaf(gl[u] * d, inv * inv, my0);
-                    my1 = fmaf(gl[u] * (d * d * inv * inv * inv - inv), 0.99f * sigmoid_f(sf[u].y), my1);
-                }
+        if (row < M) {
+            if (dsuff_in) {
+                const float2 di = __ldg(reinterpret_cast<const float2*>(dsuff_in) + row);
+                my0 = di.x;
+                my1 = di.y;
+            }
+            if (dsum_lp) {
+                // lp = -(y - mu)^2 / (2 s^2) - log s - c,  s = 0.01 + 0.99 softplus(raw):  d lp/d mu = d / s^2,
+                // d lp/d raw = (d^2 / s^3 - 1 / s) * 0.99 sigmoid(raw).  M, T, y_rows < 2^31 (checked by the entry point)
+                const float2 sf = __ldg(reinterpret_cast<const float2*>(suff) + row);
+                const float gl = __ldg(dsum_lp + (uint32_t)row / (uint32_t)T);
+                const float yv = __ldg(y + (uint32_t)row % (uint32_t)y_rows);
+                const float sc = 0.01f + 0.99f * softplus_f(sf.y), inv = 1.f / sc;
+                const float d = yv - sf.x;
+                my0 = fmaf(gl * d, inv * inv, my0);
+                my1 = fmaf(gl * (d * d * inv * inv * inv - inv), 0.99f * sigmoid_f(sf.y), my1);
             }
         }
+        const int nr = (int)min((int64_t)32, M - base);
+        constexpr int U = 4;
+        for (int r0 = 0; r0 < nr; r0 += U) {
+            float4 hv[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const float d0 = __shfl_sync(0xffffffffu, my0, u), d1 = __shfl_sync(0xffffffffu, my1, u);
-            if (!okr[u]) continue;
-            const int64_t row = row0 + u * wstride;
-            float4 o;
-            o.x = fmaf(d0, w0.x, d1 * w1.x); o.y = fmaf(d0, w0.y, d1 * w1.y);
-            o.z = fmaf(d0, w0.z, d1 * w1.z); o.w = fmaf(d0, w0.w, d1 * w1.w);
-            if (masked) {
-                if (!(hv[u].x > 0.f)) o.x = 0.f;
-                if (!(hv[u].y > 0.f)) o.y = 0.f;
-                if (!(hv[u].z > 0.f)) o.z = 0.f;
-                if (!(hv[u].w > 0.f)) o.w = 0.f;
+            for (int u = 0; u < U; ++u)
+                if (r0 + u < nr) hv[u] = __ldg(reinterpret_cast<const float4*>(h + (base + r0 + u) * ldh) + lane);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (r0 + u >= nr) break;
+                const float d0 = __shfl_sync(0xffffffffu, my0, r0 + u), d1 = __shfl_sync(0xffffffffu, my1, r0 + u);
+                float4 o;
+                o.x = fmaf(d0, w0.x, d1 * w1.x); o.y = fmaf(d0, w0.y, d1 * w1.y);
+                o.z = fmaf(d0, w0.z, d1 * w1.z); o.w = fmaf(d0, w0.w, d1 * w1.w);
+                if (masked) {
+                    if (!(hv[u].x > 0.f)) o.x = 0.f;
+                    if (!(hv[u].y > 0.f)) o.y = 0.f;
+                    if (!(hv[u].z > 0.f)) o.z = 0.f;
+                    if (!(hv[u].w > 0.f)) o.w = 0.f;
+                }
+                if (g) __stcs(reinterpret_cast<float4*>(g + (base + r0 + u) * 128) + lane, o);
+                a0.x = fmaf(d0, hv[u].x, a0.x); a0.y = fmaf(d0, hv[u].y, a0.y); a0.z = fmaf(d0, hv[u].z, a0.z); a0.w = fmaf(d0, hv[u].w, a0.w);
+                a1.x = fmaf(d1, hv[u].x, a1.x); a1.y = fmaf(d1, hv[u].y, a1.y); a1.z = fmaf(d1, hv[u].z, a1.z); a1.w = fmaf(d1, hv[u].w, a1.w);
+                b0 += d0;
+                b1 += d1;
             }
-            if (g) __stcs(reinterpret_cast<float4*>(g + row * 128) + lane, o);
-            a0.x = fmaf(d0, hv[u].x, a0.x); a0.y = fmaf(d0, hv[u].y, a0.y); a0.z = fmaf(d0, hv[u].z, a0.z); a0.w = fmaf(d0, hv[u].w, a0.w);
-            a1.x = fmaf(d1, hv[u].x, a1.x); a1.y = fmaf(d1, hv[u].y, a1.y); a1.z = fmaf(d1, hv[u].z, a1.z); a1.w = fmaf(d1, hv[u].w, a1.w);
-            b0 += d0;
-            b1 += d1;
         }
     }
     float* r = red[warp];
@@ -139,7 +136,7 @@ int npfk_nll_head_bwd(const float* h, int64_t ldh, const float* head_w, const fl
                      (reinterpret_cast<uintptr_t>(suff) & 7) == 0 && (reinterpret_cast<uintptr_t>(dsuff_in) & 7) == 0,
                  "nll_head_bwd: h / g / head_w must be 16-byte aligned (row pitch a multiple of 4 floats), suff 8-byte aligned");
     if (M <= 0) return NPFK_OK;
-    int64_t blocks = ceil_div64(M, kHbWarps * 16);       // >= 16 rows per warp so the block reduction amortises
+    int64_t blocks = ceil_div64(M, kHbWarps * 32);       // a warp takes 32 rows per iteration
     if (blocks > (int64_t)kNumSMs * 6) blocks = (int64_t)kNumSMs * 6;
     if (blocks < 1) blocks = 1;
     NPFK_LAUNCH(nll_head_bwd_kernel, (unsigned)blocks, kHbWarps * 32, 0, as_stream(stream), h, ldh, head_w, suff, y,

@@ -7,6 +7,8 @@
 //   expand  : out[m, :W] = act/mask( bias + res + sum_s T[m,s] * Wt[s, :W] )      forward K<=4, dgrad N<=4
 //   rowdot  : out[m, :S] = act( bias + sum_w X[m,w] * Wt[s,w] )                    forward N<=4, dgrad K<=4
 //   reduce  : out[s, w] += sum_m T[m,s] * X[m,w]  (+ column sums)                   wgrad with N<=4 or K<=4
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace npfk {
@@ -330,6 +332,16 @@ int skinny_linear_bwd_dx(const float* g, int64_t ldg, const float* w, int64_t ld
     return 0;
 }
 
+static int sk_reduce_ctas_per_sm() {
+    static int v = -1;      // NPFK_SKINNY_REDUCE_CTAS (developer knob)
+    if (v < 0) {
+        const char* e = getenv("NPFK_SKINNY_REDUCE_CTAS");
+        v = e ? atoi(e) : 6;      // 40 registers x 256 threads: six CTAs are resident per SM, so 6 x 148 CTAs are exactly one wave
+        if (v < 1) v = 1;      // (4: 124 us, 6: 96 us, 8: 129 us -- a third of a second wave --, 12: 99 us for 537 MB)
+    }
+    return v;
+}
+
 int skinny_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ldx, float* dw, int64_t lddw, float* db,
                          int64_t M, int N, int K, cudaStream_t st) {
     if (M <= 0) return 0;
@@ -352,8 +364,8 @@ int skinny_linear_bwd_dw(const float* g, int64_t ldg, const float* x, int64_t ld
         return 0;
     }
     a.S = S;
-    int64_t ctas = ceil_div64(M, 64);         // at least 64 rows per CTA, at most four CTAs per SM
-    if (ctas > (int64_t)kNumSMs * 4) ctas = (int64_t)kNumSMs * 4;
+    int64_t ctas = ceil_div64(M, 64);         // at least 64 rows per CTA, at most kSkReduceCtasPerSm CTAs per SM
+    if (ctas > (int64_t)kNumSMs * sk_reduce_ctas_per_sm()) ctas = (int64_t)kNumSMs * sk_reduce_ctas_per_sm();
     a.rows_per_cta = ceil_div64(M, ctas);
     ctas = ceil_div64(M, a.rows_per_cta);
     const size_t smem = sizeof(float) * ((size_t)(S + 1) * a.W + S);

@@ -27,3 +27,9 @@ def fb():
     yy = Kn.linear(x, w, b, relu=True)
     yy.backward(dy)
 print(f"fwd+bwd: {t(fb):.1f} us")
+import ctypes
+from npf_gwwaveform_b200._lib import LIB
+p = lambda t_: ctypes.c_void_p(t_.data_ptr()) if t_ is not None else None
+dw, db = torch.zeros(128, 1, device="cuda"), torch.zeros(128, device="cuda")
+st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+print(f"reduce (wgrad of the 1 -> 128 layer): {t(lambda: LIB.call('npfk_linear_bwd_dw', p(dy), 128, p(x), 1, p(dw), 1, p(db), M, 128, 1, 1, st)):.1f} us")
