@@ -10,7 +10,7 @@ python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-secondary > /dev/nul
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/${T}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-secondary > gpurun_out/${T}_ncu_bench.log 2>&1; echo "launch list rc=$?"
 python tools/ncu_targets.py > /dev/null 2>&1 && \
-ncu --set full --clock-control none -k 'regex:tc_gemm|tc_linear|tc_mlp_chain|tc_chain_bwd|nll_head|attn_|setconv_|gauss_nll|add_layernorm' -c 80 \
+ncu --set full --clock-control none -k 'regex:tc_gemm|tc_linear|tc_mlp_chain|tc_chain_bwd|nll_head|attn_|setconv_|gauss_nll|add_layernorm|skinny_' -c 100 \
     -o /tmp/${T}_full -f python tools/ncu_targets.py > gpurun_out/${T}_ncu_full.log 2>&1; echo "full rc=$?"
 ncu -i /tmp/${T}_full.ncu-rep --page raw --csv > gpurun_out/${T}_full_raw.csv 2>/dev/null; echo "raw csv rc=$?"
 ls -la gpurun_out/ /tmp/${T}_full.ncu-rep

@@ -94,3 +94,11 @@ for _ in range(2):
     lp = Kn.gauss_sum_log_prob(suff, yt)
     lp.sum().backward()
 torch.cuda.synchronize()
+# the 1 -> 128 first layer of the x encoder on the target rows: streaming expand forward, one-wave reduce (wgrad)
+x1 = torch.rand(M, 1, device="cuda") * 2 - 1
+w1s = torch.randn(128, 1, device="cuda", requires_grad=True)
+b1s = torch.zeros(128, device="cuda", requires_grad=True)
+for _ in range(2):
+    y1 = Kn.linear(x1, w1s, b1s, relu=False)
+    y1.backward(dy)
+torch.cuda.synchronize()
