@@ -15,6 +15,7 @@ from ..utils.initialization import weights_init
 from .blocks import MLP
 
 _USE_STASH = os.environ.get("NPFK_LN_STASH", "1") != "0"   # developer switch for A/B timing
+_FUSE_LN2_RESIDUAL = os.environ.get("NPFK_LN2_RESIDUAL", "1") != "0"   # developer switch for A/B timing
 
 __all__ = ["get_attender", "DotAttender", "MultiheadAttender", "TransformerAttender", "ScoreAttender",
            "MultiplicativeAttender", "AdditiveAttender", "CosineAttender", "DistanceAttender"]
@@ -258,4 +259,9 @@ class TransformerAttender(MultiheadAttender):
         stash = K.GradStash() if torch.is_grad_enabled() and _USE_STASH else None
         c = K.add_layernorm(ctx, queries, ln1.weight, ln1.bias, ln1.eps, extra=stash, park_b=q_stash,
                             attn_of=d_stash)   # residual on the raw queries
+        if _FUSE_LN2_RESIDUAL and type(self.mlp) is MLP and self.mlp.is_plain_relu_chain():
+            # c + MLP(c) leaves the MLP's last layer (residual added in its epilogue) instead of being formed by LN2 from
+            # two tensors: LN2 reads one tensor instead of two, forward and backward.  The same bits (one fp32 addition of
+            # the same two operands); the gradient of the residual use of c goes through the stash as before.
+            return K.add_layernorm(self.mlp(c, res=c, res_stash=stash), None, ln2.weight, ln2.bias, ln2.eps)
         return K.add_layernorm(c, self.mlp(c), ln2.weight, ln2.bias, ln2.eps, park_a=stash)

@@ -66,9 +66,10 @@ class MLP(nn.Module):
         """True when the whole MLP can run as one K.mlp_chain node (ReLU, no dropout, no residual links)."""
         return isinstance(self.activation, nn.ReLU) and isinstance(self.dropout, nn.Identity) and not self.is_res
 
-    def forward(self, x, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None):
+    def forward(self, x, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None, res_stash=None):
         """``res`` / ``out_relu`` fuse ``relu(res + MLP(x))`` (the sum-merge) into the last layer's epilogue.
         ``x_is_relu`` / ``dy_premasked``: see kernels._MlpChainFn (ReLU backward fused across the sum-merge).
+        ``res_stash``: a kernels.GradStash that takes the gradient of ``res`` instead of autograd (plain ReLU chains only).
         ``nll=(y, T)`` (decoders only; see ``accepts_nll``): returns ``(out, sum_lp or None)``, the Gaussian
         log-likelihood of y under the predictive distribution summed over the T rows of each task, evaluated in the
         chain kernel's epilogue."""
@@ -77,8 +78,8 @@ class MLP(nn.Module):
             layers += [(lin.weight, lin.bias) for lin in self.linears]
             layers.append((self.out.weight, self.out.bias))
             return K.mlp_chain(x, layers, res=res, out_relu=out_relu, x_is_relu=x_is_relu, dy_premasked=dy_premasked,
-                               nll=nll)
-        assert not (x_is_relu or dy_premasked or nll is not None)
+                               nll=nll, res_stash=res_stash)
+        assert not (x_is_relu or dy_premasked or nll is not None or res_stash is not None)
         h = self.dropout(self._hidden(self.to_hidden, x))
         for lin in self.linears:
             o = self._hidden(lin, h)

@@ -397,7 +397,7 @@ class _MlpChainFn(Function):
     """
 
     @staticmethod
-    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, nll, grad_enabled: bool, x, res, *wb):
+    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, nll, grad_enabled: bool, res_stash, x, res, *wb):
         require_cuda(x, res, *wb)
         ctx.set_materialize_grads(False)
         n_layers = len(wb) // 2
@@ -498,6 +498,7 @@ class _MlpChainFn(Function):
                    None if res is None else res.shape, [wb[2 * i + 1] is not None for i in range(n_layers)], x.shape,
                    head_fused, nll_saved)
         ctx.wb = wb
+        ctx.res_stash = res_stash
         if training:
             ctx.save_for_backward(h if (out_relu and not dy_premasked) or head_fused else None, *acts, *wvs,
                                   nll_saved[0] if nll_saved is not None else None)
@@ -525,17 +526,22 @@ class _MlpChainFn(Function):
             LIB.call("npfk_relu_bwd", _p(g), N_out, _p(y_out), N_out, _p(g2), N_out, M, N_out, st)
             g = g2
         dres = None
-        if has_res and ctx.needs_input_grad[6]:
+        if has_res and ctx.needs_input_grad[7]:
             res_rows = dims[-1][4]
             if res_rows == M:
                 dres = g.reshape(res_shape)
             else:
                 dres = torch.empty(res_shape, device=g.device, dtype=torch.float32)
                 LIB.call("npfk_rows_fold_sum", _p(g), N_out, _p(dres), N_out, res_rows, M // res_rows, N_out, st)
+        if dres is not None and ctx.res_stash is not None:
+            # the residual is another use of a tensor whose producer collects its gradients through a GradStash (the
+            # transformer block: c feeds the MLP and, as the residual of its last layer, LN2): hand it over there instead
+            # of returning it, so autograd does not sum two [M, 128] tensors in a separate pass
+            ctx.res_stash.t, dres = dres, None
         grads_wb = [None] * (2 * n_layers)
 
         def need_w_of(i):
-            return ctx.needs_input_grad[7 + 2 * i] or (has_b[i] and ctx.needs_input_grad[8 + 2 * i])
+            return ctx.needs_input_grad[8 + 2 * i] or (has_b[i] and ctx.needs_input_grad[9 + 2 * i])
 
         sunk = []       # parameters whose gradients the next launch writes straight into the trainer's flat buffer
 
@@ -545,8 +551,8 @@ class _MlpChainFn(Function):
             is enqueued: a pair launch (K1b) covers four parameters, and a callback that ran before the launch could make
             the trainer all-reduce a bucket that ends inside the pair before its gradients exist."""
             N, Kd = dims[i][0], dims[i][1]
-            sink_w = _grad_sink_buf(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[7 + 2 * i] else None
-            sink_b = _grad_sink_buf(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[8 + 2 * i] else None
+            sink_w = _grad_sink_buf(ctx.wb[2 * i], (N, Kd)) if ctx.needs_input_grad[8 + 2 * i] else None
+            sink_b = _grad_sink_buf(ctx.wb[2 * i + 1]) if has_b[i] and ctx.needs_input_grad[9 + 2 * i] else None
             sunk.extend(prm for prm, buf in ((ctx.wb[2 * i], sink_w), (ctx.wb[2 * i + 1], sink_b)) if buf is not None)
             dw = sink_w if sink_w is not None else torch.zeros(N, Kd, device=dev, dtype=torch.float32)
             db = None
@@ -572,7 +578,7 @@ class _MlpChainFn(Function):
             N, Kd, ldh, ldw, _ = dims[i]
             hin = acts[i]
             need_w = need_w_of(i)
-            need_dx = i > 0 or ctx.needs_input_grad[5]
+            need_dx = i > 0 or ctx.needs_input_grad[6]
             masked = i > 0 or x_is_relu
             if head_fused and i == n_layers - 1 and M > 0:
                 # decoder tail: d(log-likelihood)/d(suff), the head's dgrad (+ ReLU mask of the layer below) and its
@@ -592,7 +598,7 @@ class _MlpChainFn(Function):
                 continue
             # K1b: two consecutive 128 -> 128 layers in one kernel -- the gradient between them stays on the SM
             if (pair_ok and i >= 1 and square(i) and square(i - 1) and need_w and need_w_of(i - 1)
-                    and (i - 1 > 0 or ctx.needs_input_grad[5]) and ldh % 4 == 0 and dims[i - 1][2] % 4 == 0
+                    and (i - 1 > 0 or ctx.needs_input_grad[6]) and ldh % 4 == 0 and dims[i - 1][2] % 4 == 0
                     and hin.data_ptr() % 16 == 0 and acts[i - 1].data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0):
                 dw1, db1 = wgrad_buffers(i)
                 dw0, db0 = wgrad_buffers(i - 1)
@@ -629,11 +635,11 @@ class _MlpChainFn(Function):
                          _p(dx), Kd, M, N, Kd, mode, st)
             g = dx
             i -= 1
-        dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[5]) else None
-        return (None, None, None, None, None, dx, dres, *grads_wb)
+        dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[6]) else None
+        return (None, None, None, None, None, None, dx, dres, *grads_wb)
 
 
-def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None):
+def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None, res_stash=None):
     """ReLU MLP over `layers` = [(weight, bias), ...] as a single autograd node (see _MlpChainFn).  ``nll=(y, T)``:
     returns ``(out, sum_lp)`` where sum_lp[m // T] = sum of log N(y; loc, scale) over the T rows of a task, or
     ``(out, None)`` when the tail could not ride in the fused chain (the caller then uses gauss_sum_log_prob)."""
@@ -642,7 +648,7 @@ def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked
         flat += [w, b]
     # Function.forward cannot see the caller's grad mode (needs_input_grad ignores no_grad): pass it, so that inference
     # keeps nothing for a backward pass and writes only the chain's result
-    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, nll, torch.is_grad_enabled(), x, res, *flat)
+    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, nll, torch.is_grad_enabled(), res_stash, x, res, *flat)
 
 
 # ------------------------------------------------------------------------------------------ broadcast merge
