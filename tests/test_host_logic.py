@@ -112,6 +112,31 @@ def test_cabi_rejects_bad_arguments_without_gpu():
         LIB.call("npfk_mha_fwd", p, p, p, p, p, 1, 4, 4, 1, 5, 1.0, 0, None)
 
 
+def test_cabi_round2_entry_points_reject_bad_arguments_without_gpu():
+    """argument checks of the entry points added in round 2 run before anything touches the device, and the positions
+    that kernels.KernelTimer reads (`_work`) are the ones include/npfk.h declares"""
+    from npf_gwwaveform_b200 import _lib
+    from npf_gwwaveform_b200._lib import LIB, NpfkError
+
+    protos = _lib.parse_header()
+    names = [n for _, n in protos["npfk_linear_bwd_fused2"][1]]
+    assert names.index("M") == 19 and names.index("flags") == 10 and names[-1] == "stream"
+    assert [n for _, n in protos["npfk_bn_stats_static"][1]][:4] == ["x", "rows", "C", "stats"]
+    p = ctypes.c_void_p(256)
+    with pytest.raises(NpfkError, match="null pointer"):
+        LIB.call("npfk_linear_bwd_fused2", None, 128, p, 128, p, 128, p, 128, p, 128, 0, p, 128, p, 128, None, p, 128, None,
+                 256, None)
+    with pytest.raises(NpfkError, match="unknown flag"):
+        LIB.call("npfk_linear_bwd_fused2", p, 128, p, 128, p, 128, p, 128, p, 128, 4, p, 128, p, 128, None, p, 128, None,
+                 256, None)
+    with pytest.raises(NpfkError, match="M >= 128"):      # too few rows for the tensor-core tile: the caller falls back
+        LIB.call("npfk_linear_bwd_fused2", p, 128, p, 128, p, 128, p, 128, p, 128, 1, p, 128, p, 128, None, p, 128, None,
+                 64, None)
+    with pytest.raises(NpfkError, match="4096"):          # the static scratch has a stated maximum
+        LIB.call("npfk_bn_stats_static", p, 8, 4097, p, None, None, 0.0, None, None)
+    assert LIB.launch_count() == 0
+
+
 def test_datasplit_host_rules():
     """number-of-points rules of GetRandomIndcs (datasplit.py:106-126) and the no-host-path error"""
     import random
