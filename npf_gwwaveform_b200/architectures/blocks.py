@@ -4,6 +4,7 @@ Same constructor signatures, attribute names and ``state_dict`` layout as the re
 (npf/architectures/mlp.py:12-115, npf/architectures/encoders.py:105-213); the arithmetic runs in the
 npfk kernels (fused bias + ReLU (+ residual) epilogues) instead of addmm + separate elementwise kernels.
 """
+import os
 import warnings
 
 import torch
@@ -13,6 +14,8 @@ from .. import kernels as K
 from ..utils.initialization import hidden_linear_init_, linear_init, output_linear_init_, weights_init
 
 __all__ = ["MLP", "MergeFlatInputs", "merge_flat_input", "DiscardIthArg", "discard_ith_arg"]
+
+_ONE_CHAIN_MERGE = os.environ.get("NPFK_ONE_CHAIN_MERGE", "1") != "0"   # developer switch for A/B timing
 
 
 class MLP(nn.Module):
@@ -66,6 +69,13 @@ class MLP(nn.Module):
         """True when the whole MLP can run as one K.mlp_chain node (ReLU, no dropout, no residual links)."""
         return isinstance(self.activation, nn.ReLU) and isinstance(self.dropout, nn.Identity) and not self.is_res
 
+    def layer_list(self):
+        """[(weight, bias), ...] in forward order (what kernels.mlp_chain takes)"""
+        layers = [(self.to_hidden.weight, self.to_hidden.bias)]
+        layers += [(lin.weight, lin.bias) for lin in self.linears]
+        layers.append((self.out.weight, self.out.bias))
+        return layers
+
     def forward(self, x, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None, res_stash=None):
         """``res`` / ``out_relu`` fuse ``relu(res + MLP(x))`` (the sum-merge) into the last layer's epilogue.
         ``x_is_relu`` / ``dy_premasked``: see kernels._MlpChainFn (ReLU backward fused across the sum-merge).
@@ -74,10 +84,7 @@ class MLP(nn.Module):
         log-likelihood of y under the predictive distribution summed over the T rows of each task, evaluated in the
         chain kernel's epilogue."""
         if self.is_plain_relu_chain():
-            layers = [(self.to_hidden.weight, self.to_hidden.bias)]
-            layers += [(lin.weight, lin.bias) for lin in self.linears]
-            layers.append((self.out.weight, self.out.bias))
-            return K.mlp_chain(x, layers, res=res, out_relu=out_relu, x_is_relu=x_is_relu, dy_premasked=dy_premasked,
+            return K.mlp_chain(x, self.layer_list(), res=res, out_relu=out_relu, x_is_relu=x_is_relu, dy_premasked=dy_premasked,
                                nll=nll, res_stash=res_stash)
         assert not (x_is_relu or dy_premasked or nll is not None or res_stash is not None)
         h = self.dropout(self._hidden(self.to_hidden, x))
@@ -153,12 +160,24 @@ class MergeFlatInputs(nn.Module):
             return K.bcast_add_relu(x1, r)     # (the caller applies flat_module, with nll when asked)
         # Case B: same rows (x2 possibly with a leading n_z dim that x1 is tiled over): fuse into the epilogue
         if x2.shape[-x1.dim():-1] == x1.shape[:-1] and x2.dim() in (x1.dim(), x1.dim() + 1):
+            if self._one_chain():
+                # resizer and flat module as ONE chain node: relu(x1 + resizer(x2)) is a hidden layer with a residual, the
+                # merged activation is written once (for backward) and never read back in forward; in fast mode a single
+                # kernel launch (K1) up to the head and the log-likelihood tail
+                layers = self.resizer.layer_list()
+                return K.mlp_chain(x2, layers + self.flat_module.layer_list(), res=x1, res_layer=len(layers) - 1,
+                                   nll=nll), True
             if self._fused_relu_bwd():
                 # merged feeds only flat_module, whose first dgrad masks with merged > 0: the resizer skips its own
                 merged = self.resizer(x2, res=x1, out_relu=True, dy_premasked=True)
                 return self.flat_module(merged, x_is_relu=True, nll=nll), True
             return self.resizer(x2, res=x1, out_relu=True)
         return torch.relu(x1 + self.resizer(x2))                     # exotic broadcasting: plain composition
+
+    def _one_chain(self):
+        fm = self.flat_module
+        return (_ONE_CHAIN_MERGE and type(fm) is MLP and fm.is_plain_relu_chain() and type(self.resizer) is MLP
+                and self.resizer.is_plain_relu_chain())
 
     def _fused_relu_bwd(self):
         fm = self.flat_module

@@ -367,7 +367,7 @@ def _ptr_array(ts):
     return (ctypes.c_void_p * len(ts))(*[None if t is None else t.data_ptr() for t in ts])
 
 
-def _chain_fwd(x, ldx, M, ws, bs, relus, res, res_rows, outs, head=None, nll=None):
+def _chain_fwd(x, ldx, M, ws, bs, relus, res, res_rows, outs, head=None, nll=None, res_layer=None):
     """one launch of npfk_mlp_chain_fwd over consecutive 128 -> 128 layers; `outs[l]` None = that activation stays on
     chip.  head = (w[2,128], b or None, suff[M,2]); nll = (y, y_rows, T, sum_lp)."""
     L = len(ws)
@@ -375,7 +375,7 @@ def _chain_fwd(x, ldx, M, ws, bs, relus, res, res_rows, outs, head=None, nll=Non
     hw, hb, suff = head if head is not None else (None, None, None)
     y, y_rows, T, sum_lp = nll if nll is not None else (None, 0, 0, None)
     LIB.call("npfk_mlp_chain_fwd", _p(x), ldx, M, L, _ptr_array(ws), _ptr_array(bs), relu_mask,
-             (L - 1) if res is not None else -1, _p(res), _CHAIN_DIM, res_rows, _ptr_array(outs), _p(hw), _p(hb), _p(suff),
+             ((L - 1) if res_layer is None else res_layer) if res is not None else -1, _p(res), _CHAIN_DIM, res_rows, _ptr_array(outs), _p(hw), _p(hb), _p(suff),
              _p(y), y_rows, T, _p(sum_lp), MODE_FAST, _st())
 
 
@@ -397,10 +397,15 @@ class _MlpChainFn(Function):
     """
 
     @staticmethod
-    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, nll, grad_enabled: bool, res_stash, x, res, *wb):
+    def forward(ctx, out_relu: bool, x_is_relu: bool, dy_premasked: bool, nll, grad_enabled: bool, res_opts, x, res, *wb):
         require_cuda(x, res, *wb)
         ctx.set_materialize_grads(False)
         n_layers = len(wb) // 2
+        # res_opts = (GradStash that takes the residual's gradient or None, index of the layer whose pre-activation gets
+        # + res or None = the last one)
+        res_stash, res_at = res_opts if res_opts is not None else (None, None)
+        if res_at is None:
+            res_at = n_layers - 1
         mode = _state["mode"]
         lead = x.shape[:-1]
         M = 1
@@ -423,10 +428,11 @@ class _MlpChainFn(Function):
         sq = [d[0] == _CHAIN_DIM and d[1] == _CHAIN_DIM and d[3] == _CHAIN_DIM for d in dims]
         fuse_ok = (mode == MODE_FAST and _state.get("chain_fusion", True) and M >= 128)
         resv, res_rows = None, 0
-        N_last = dims[-1][0]
         if res is not None:
+            if not 0 <= res_at < n_layers:
+                raise NpfkError(f"mlp: residual layer {res_at} outside the chain of {n_layers} layers")
             resv = _c(res)
-            res_rows = resv.numel() // N_last
+            res_rows = resv.numel() // dims[res_at][0]
             if res_rows == 0 or M % max(res_rows, 1) != 0:
                 raise NpfkError(f"mlp: residual rows {res_rows} do not tile M={M}")
         head_fused, suff, sum_lp, nll_saved = False, None, None, None
@@ -437,14 +443,14 @@ class _MlpChainFn(Function):
                 while j < n_layers and sq[j] and j - i < _CHAIN_MAX:
                     j += 1
             # the decoder head: a final 128 -> 2 layer without ReLU or residual rides in the chain's epilogue
-            with_head = (j > i and j == n_layers - 1 and dims[j][0] == 2 and dims[j][1] == _CHAIN_DIM and res is None
+            with_head = (j > i and j == n_layers - 1 and dims[j][0] == 2 and dims[j][1] == _CHAIN_DIM
+                         and (res is None or res_at != j)
                          and not out_relu and wvs[j].is_contiguous())
             if j - i >= 2 or (with_head and j - i >= 1):
                 relus = [True] * (j - i)
-                r_here = None
-                if j == n_layers:               # the run ends the chain: output activation and residual are the caller's
+                if j == n_layers:               # the run ends the chain: the output activation is the caller's
                     relus[-1] = bool(out_relu)
-                    r_here = resv
+                r_here = resv if (resv is not None and i <= res_at < j) else None     # the residual lands in this run
                 outs = []
                 for l in range(i, j):
                     keep = training or l == j - 1
@@ -463,10 +469,10 @@ class _MlpChainFn(Function):
                         nl = (yv, yv.numel(), T, sum_lp)
                         nll_saved = (yv, T)
                 _chain_fwd(h, ldh, M, wvs[i:j], [_c(wb[2 * l + 1]) for l in range(i, j)], relus, r_here, res_rows, outs,
-                           head, nl)
+                           head, nl, res_layer=res_at - i)
                 for l in range(i, j):
                     dims[l][2] = ldh if l == i else _CHAIN_DIM
-                    dims[l][4] = res_rows if (r_here is not None and l == j - 1) else 0
+                    dims[l][4] = res_rows if (r_here is not None and l == res_at) else 0
                     if l > i:
                         acts.append(outs[l - i - 1])
                 h, ldh = outs[-1], _CHAIN_DIM
@@ -485,18 +491,19 @@ class _MlpChainFn(Function):
             last = i == n_layers - 1
             bv = _c(wb[2 * i + 1])
             y = torch.empty(M, N, device=x.device, dtype=torch.float32)
+            here = resv is not None and i == res_at
             if M > 0:
-                LIB.call("npfk_linear_fwd", _p(h), ldh, _p(wvs[i]), dims[i][3], _p(bv), _p(resv if last else None), N,
-                         res_rows if last else 0, _p(y), N, M, N, Kd, int(out_relu if last else True), mode, st)
+                LIB.call("npfk_linear_fwd", _p(h), ldh, _p(wvs[i]), dims[i][3], _p(bv), _p(resv if here else None), N,
+                         res_rows if here else 0, _p(y), N, M, N, Kd, int(out_relu if last else True), mode, st)
             dims[i][2] = ldh
-            dims[i][4] = res_rows if last else 0
+            dims[i][4] = res_rows if here else 0
             h, ldh = y, N
             if not last:
                 acts.append(y)
             i += 1
         ctx.cfg = (out_relu, x_is_relu, dy_premasked, mode, M, n_layers, [tuple(d) for d in dims], res is not None,
                    None if res is None else res.shape, [wb[2 * i + 1] is not None for i in range(n_layers)], x.shape,
-                   head_fused, nll_saved)
+                   head_fused, nll_saved, res_at)
         ctx.wb = wb
         ctx.res_stash = res_stash
         if training:
@@ -512,7 +519,7 @@ class _MlpChainFn(Function):
     @staticmethod
     def backward(ctx, dy, dsum_lp=None):
         (out_relu, x_is_relu, dy_premasked, mode, M, n_layers, dims, has_res, res_shape, has_b, x_shape, head_fused,
-         nll_saved) = ctx.cfg
+         nll_saved, res_at) = ctx.cfg
         saved = ctx.saved_tensors
         y_out, acts, wvs, y_nll = saved[0], saved[1:1 + n_layers], saved[1 + n_layers:1 + 2 * n_layers], saved[-1]
         st = _st()
@@ -525,19 +532,19 @@ class _MlpChainFn(Function):
             g2 = torch.empty_like(g)
             LIB.call("npfk_relu_bwd", _p(g), N_out, _p(y_out), N_out, _p(g2), N_out, M, N_out, st)
             g = g2
-        dres = None
-        if has_res and ctx.needs_input_grad[7]:
-            res_rows = dims[-1][4]
+        need_dres = has_res and ctx.needs_input_grad[7]
+
+        def residual_grad(gr):
+            """gradient of the residual = the (masked) gradient of the pre-activation it was added to, summed over the rows
+            that shared it"""
+            res_rows, Nr = dims[res_at][4], dims[res_at][0]
             if res_rows == M:
-                dres = g.reshape(res_shape)
-            else:
-                dres = torch.empty(res_shape, device=g.device, dtype=torch.float32)
-                LIB.call("npfk_rows_fold_sum", _p(g), N_out, _p(dres), N_out, res_rows, M // res_rows, N_out, st)
-        if dres is not None and ctx.res_stash is not None:
-            # the residual is another use of a tensor whose producer collects its gradients through a GradStash (the
-            # transformer block: c feeds the MLP and, as the residual of its last layer, LN2): hand it over there instead
-            # of returning it, so autograd does not sum two [M, 128] tensors in a separate pass
-            ctx.res_stash.t, dres = dres, None
+                return gr.reshape(res_shape)
+            out = torch.empty(res_shape, device=gr.device, dtype=torch.float32)
+            LIB.call("npfk_rows_fold_sum", _p(gr), Nr, _p(out), Nr, res_rows, M // res_rows, Nr, st)
+            return out
+
+        dres = residual_grad(g) if (need_dres and res_at == n_layers - 1) else None
         grads_wb = [None] * (2 * n_layers)
 
         def need_w_of(i):
@@ -577,6 +584,8 @@ class _MlpChainFn(Function):
         while i >= 0:
             N, Kd, ldh, ldw, _ = dims[i]
             hin = acts[i]
+            if need_dres and i == res_at and i < n_layers - 1:
+                dres = residual_grad(g)      # a residual inside the chain (decoder: resizer + flat module as one node)
             need_w = need_w_of(i)
             need_dx = i > 0 or ctx.needs_input_grad[6]
             masked = i > 0 or x_is_relu
@@ -598,6 +607,7 @@ class _MlpChainFn(Function):
                 continue
             # K1b: two consecutive 128 -> 128 layers in one kernel -- the gradient between them stays on the SM
             if (pair_ok and i >= 1 and square(i) and square(i - 1) and need_w and need_w_of(i - 1)
+                    and not (need_dres and res_at == i - 1)      # that gradient must reach HBM: it is the residual's
                     and (i - 1 > 0 or ctx.needs_input_grad[6]) and ldh % 4 == 0 and dims[i - 1][2] % 4 == 0
                     and hin.data_ptr() % 16 == 0 and acts[i - 1].data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0):
                 dw1, db1 = wgrad_buffers(i)
@@ -635,20 +645,29 @@ class _MlpChainFn(Function):
                          _p(dx), Kd, M, N, Kd, mode, st)
             g = dx
             i -= 1
+        if dres is not None and ctx.res_stash is not None:
+            # the residual is another use of a tensor whose producer collects its gradients through a GradStash (the
+            # transformer block: c feeds the MLP and, as the residual of its last layer, LN2): hand it over there instead
+            # of returning it, so autograd does not sum two [M, 128] tensors in a separate pass
+            ctx.res_stash.t, dres = dres, None
         dx = g.reshape(x_shape) if (g is not None and ctx.needs_input_grad[6]) else None
         return (None, None, None, None, None, None, dx, dres, *grads_wb)
 
 
-def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None, res_stash=None):
+def mlp_chain(x, layers, res=None, out_relu=False, x_is_relu=False, dy_premasked=False, nll=None, res_stash=None,
+              res_layer=None):
     """ReLU MLP over `layers` = [(weight, bias), ...] as a single autograd node (see _MlpChainFn).  ``nll=(y, T)``:
     returns ``(out, sum_lp)`` where sum_lp[m // T] = sum of log N(y; loc, scale) over the T rows of a task, or
-    ``(out, None)`` when the tail could not ride in the fused chain (the caller then uses gauss_sum_log_prob)."""
+    ``(out, None)`` when the tail could not ride in the fused chain (the caller then uses gauss_sum_log_prob).
+    ``res`` is added to the pre-activation of layer ``res_layer`` (default: the last one; a hidden layer applies its ReLU
+    after the sum -- the decoder's ``relu(x1 + resizer(x2))`` followed by its flat module is one such chain)."""
     flat = []
     for w, b in layers:
         flat += [w, b]
     # Function.forward cannot see the caller's grad mode (needs_input_grad ignores no_grad): pass it, so that inference
     # keeps nothing for a backward pass and writes only the chain's result
-    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, nll, torch.is_grad_enabled(), res_stash, x, res, *flat)
+    return _MlpChainFn.apply(out_relu, x_is_relu, dy_premasked, nll, torch.is_grad_enabled(), (res_stash, res_layer), x,
+                             res, *flat)
 
 
 # ------------------------------------------------------------------------------------------ broadcast merge
