@@ -393,6 +393,11 @@ class _MlpChainFn(Function):
     (npfk_mlp_chain_fwd: activations stay in tensor memory, only what backward needs is written), and a final 128 -> 2
     layer (the decoder head) is evaluated in that kernel's epilogue.  ``nll = (y, T)`` additionally makes the node
     return ``sum_t log N(y; loc, scale)`` per task as a second output (decode tail + sum_log_prob fused, north_star (4)).
+    ``res_opts = (res_stash, res_layer)``: the residual is added to the pre-activation of layer ``res_layer`` (None = the last
+    one; inside the chain the layer's ReLU follows the sum), and its gradient -- the masked gradient of that pre-activation --
+    is either returned or, with a GradStash, handed to the node that collects the other gradients of the same tensor.  In
+    backward, pairs of consecutive 128 -> 128 layers go through npfk_linear_bwd_fused2 (K1b) unless the gradient between
+    them is the residual's.
     args = (x, res, w_1, b_1, ..., w_L, b_L); b_i may be None.
     """
 
